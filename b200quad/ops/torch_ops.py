@@ -1,0 +1,39 @@
+"""torch.ops.b200quad.* — the ops registered by csrc/torch_ops.cpp."""
+import os
+
+import torch
+
+from .. import _native, models
+
+_loaded = False
+
+
+def load():
+    global _loaded
+    if not _loaded:
+        _native.load()   # core library first (RTLD_GLOBAL) so the op library resolves against it
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lib",
+                            "libb200quad_torch.so")
+        if not os.path.exists(path):
+            raise _native.NativeError("libb200quad_torch.so is not built: run `python build.py`")
+        torch.ops.load_library(path)
+        _loaded = True
+    return torch.ops.b200quad
+
+
+def integrate(f, a, b, n, rule="left", dtype="fp64", eval="auto", device=None):
+    """0-dim float64 tensor; on CUDA the work is enqueued on torch's current stream."""
+    ops = load()
+    integ, _ = models.get(f)
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else -1
+    return ops.integrate(integ.native_id, float(a), float(b), int(n), _native.RULES[rule],
+                         _native.DTYPES[dtype], _native.EVALS[eval], int(device))
+
+
+def cumulative(f, x0, dx, n, device=None):
+    ops = load()
+    integ, _ = models.get(f)
+    if device is None:
+        device = torch.cuda.current_device() if torch.cuda.is_available() else -1
+    return ops.cumulative(integ.native_id, float(x0), float(dx), int(n), int(device))

@@ -1,0 +1,289 @@
+"""Worlds: who takes part in a call and how their partial results meet.
+
+The reference spreads work over MPI ranks and combines with MPI_Send/Recv,
+MPI_Reduce, MPI_Barrier and MPI_Bcast (riemann.cpp:62-85, 4main.c:69-221).
+Here a *world* is a set of GPUs whose fused kernels publish partial results
+into each other's memory over NVLink and meet at an in-kernel barrier:
+
+  Context      one GPU of this process (world of 1)
+  LocalWorld   several GPUs driven by this one process (peer access through UVA)
+  DistWorld    one GPU per process under torchrun; torch.distributed (NCCL) is
+               only the bootstrap that carries the CUDA-IPC handles around
+  CpuWorld     torch.distributed (gloo) ranks on the CPU backend: each computes
+               its segments of the fixed tree, an all_gather moves 8 pairs
+"""
+import ctypes as C
+import os
+import threading
+
+from .. import _native
+from .._native import Job, Result, ScanJob, ScanResult, NativeError, check
+
+_lock = threading.Lock()
+_contexts = {}
+_local_worlds = {}
+_dist_world = None
+
+
+class Context:
+    """Owns every device buffer the fused kernels need on one GPU."""
+
+    def __init__(self, device=0):
+        lib, cuda = _native.load()
+        if not cuda or lib.bq_cuda_device_count() == 0:
+            raise NativeError("no CUDA device available for a b200quad Context")
+        self.lib = lib
+        self.device = int(device)
+        h = C.c_void_p()
+        check(lib.bq_ctx_create(self.device, C.byref(h)), "bq_ctx_create")
+        self.handle = h
+        self.rank, self.world = 0, 1
+        self._owned = True
+
+    @classmethod
+    def _wrap(cls, lib, handle, device, rank, world):
+        self = cls.__new__(cls)
+        self.lib, self.handle, self.device = lib, handle, device
+        self.rank, self.world = rank, world
+        self._owned = False
+        return self
+
+    # -- definite integral --------------------------------------------------
+    def integrate(self, job):
+        res = Result()
+        rc = self.lib.bq_integrate(self.handle, C.byref(job), C.byref(res))
+        check(rc, "bq_integrate")
+        return res
+
+    def integrate_async(self, job, stream=None):
+        check(self.lib.bq_integrate_async(self.handle, C.byref(job), C.c_void_p(stream or 0)),
+              "bq_integrate_async")
+
+    def fetch(self):
+        res = Result()
+        check(self.lib.bq_result_fetch(self.handle, C.byref(res)), "bq_result_fetch")
+        return res
+
+    # -- cumulative -----------------------------------------------------------
+    def cumulative(self, job, dP, dQ, dS=0):
+        res = ScanResult()
+        rc = self.lib.bq_cumulative(self.handle, C.byref(job), C.c_void_p(dP), C.c_void_p(dQ),
+                                    C.c_void_p(dS or 0), C.byref(res))
+        check(rc, "bq_cumulative")
+        return res
+
+    # -- knobs ------------------------------------------------------------------
+    def configure(self, ctas_per_sm=0, cluster=0, rows_per_tile=0):
+        check(self.lib.bq_ctx_configure(self.handle, ctas_per_sm, cluster, rows_per_tile),
+              "bq_ctx_configure")
+
+    def set_timeout_ms(self, ms):
+        check(self.lib.bq_ctx_set_timeout_ms(self.handle, int(ms)), "bq_ctx_set_timeout_ms")
+
+    def set_profile(self, table):
+        arr = (C.c_double * len(table))(*table)
+        check(self.lib.bq_ctx_set_profile(self.handle, arr, len(table)), "bq_ctx_set_profile")
+
+    def inject_fault(self, kind=1):
+        check(self.lib.bq_ctx_inject_fault(self.handle, int(kind)), "bq_ctx_inject_fault")
+
+    def reset_comm(self):
+        check(self.lib.bq_ctx_reset_comm(self.handle), "bq_ctx_reset_comm")
+
+    @property
+    def stream(self):
+        return self.lib.bq_ctx_stream(self.handle)
+
+    def close(self):
+        if getattr(self, "_owned", False) and self.handle:
+            self.lib.bq_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def context(device=None):
+    """The cached Context of a device (default: torch's current CUDA device, else 0)."""
+    if device is None:
+        device = 0
+        try:
+            import torch
+            if torch.cuda.is_available():
+                device = torch.cuda.current_device()
+        except Exception:
+            pass
+    with _lock:
+        if device not in _contexts:
+            _contexts[device] = Context(device)
+        return _contexts[device]
+
+
+class LocalWorld:
+    """`size` GPUs of this process; one launch per GPU, one host thread."""
+
+    def __init__(self, size, devices=None):
+        lib, cuda = _native.load()
+        if not cuda:
+            raise NativeError("LocalWorld needs the CUDA library")
+        self.lib = lib
+        self.size = int(size)
+        devs = list(devices) if devices is not None else list(range(self.size))
+        arr = (C.c_int * self.size)(*devs)
+        h = C.c_void_p()
+        check(lib.bq_world_create(self.size, arr, C.byref(h)), "bq_world_create")
+        self.handle = h
+        self.devices = devs
+        self.contexts = [Context._wrap(lib, C.c_void_p(lib.bq_world_ctx(h, r)), devs[r], r, self.size)
+                         for r in range(self.size)]
+
+    def integrate(self, job):
+        out = (Result * self.size)()
+        check(self.lib.bq_world_integrate(self.handle, C.byref(job), out), "bq_world_integrate")
+        return list(out)
+
+    def cumulative(self, job, dP, dQ):
+        out = (ScanResult * self.size)()
+        aP = (C.c_void_p * self.size)(*dP)
+        aQ = (C.c_void_p * self.size)(*dQ)
+        check(self.lib.bq_world_cumulative(self.handle, C.byref(job), aP, aQ, out),
+              "bq_world_cumulative")
+        return list(out)
+
+    def close(self):
+        if self.handle:
+            self.lib.bq_world_destroy(self.handle)
+            self.handle = None
+
+
+def local_world(size):
+    with _lock:
+        if size not in _local_worlds:
+            _local_worlds[size] = LocalWorld(size)
+        return _local_worlds[size]
+
+
+class DistWorld:
+    """One GPU per process (torchrun).  torch.distributed moves only the IPC handles."""
+
+    def __init__(self, group=None, device=None):
+        import torch
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            raise NativeError("torch.distributed is not initialised")
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.size = dist.get_world_size(group)
+        if device is None:
+            device = int(os.environ.get("LOCAL_RANK", self.rank % max(torch.cuda.device_count(), 1)))
+        torch.cuda.set_device(device)
+        self.ctx = context(device)
+        lib = self.ctx.lib
+        mine = C.create_string_buffer(_native.IPC_HANDLE_BYTES)
+        check(lib.bq_ctx_export_comm(self.ctx.handle, mine), "bq_ctx_export_comm")
+        gathered = [None] * self.size
+        dist.all_gather_object(gathered, bytes(mine.raw), group=group)
+        blob = b"".join(gathered)
+        check(lib.bq_ctx_attach_peers(self.ctx.handle, self.rank, self.size, blob),
+              "bq_ctx_attach_peers")
+        self.ctx.rank, self.ctx.world = self.rank, self.size
+        dist.barrier(group=group)
+
+    def integrate(self, job):
+        return self.ctx.integrate(job)
+
+    def reset(self):
+        self.ctx.reset_comm()
+        self.dist.barrier(group=self.group)
+
+    def share_tables(self, tP, tQ):
+        """Map every rank's full-size P/Q tables here (replicating scans)."""
+        lib = self.ctx.lib
+        hp = C.create_string_buffer(_native.IPC_HANDLE_BYTES)
+        hq = C.create_string_buffer(_native.IPC_HANDLE_BYTES)
+        check(lib.bq_ipc_export(C.c_void_p(tP.data_ptr()), hp), "bq_ipc_export")
+        check(lib.bq_ipc_export(C.c_void_p(tQ.data_ptr()), hq), "bq_ipc_export")
+        # cudaIpc handles address the allocation base: ship the offset too.
+        import torch
+        def base_off(t):
+            return t.data_ptr() - t.untyped_storage().data_ptr()
+        gathered = [None] * self.size
+        self.dist.all_gather_object(gathered, (bytes(hp.raw), bytes(hq.raw), base_off(tP), base_off(tQ)),
+                                    group=self.group)
+        aP = (C.c_void_p * _native.MAX_WORLD)()
+        aQ = (C.c_void_p * _native.MAX_WORLD)()
+        opened = []
+        for r, (bp, bq_, op, oq) in enumerate(gathered):
+            if r == self.rank:
+                aP[r], aQ[r] = tP.data_ptr(), tQ.data_ptr()
+                continue
+            pp, pq = C.c_void_p(), C.c_void_p()
+            check(lib.bq_ipc_open(bp, C.byref(pp)), "bq_ipc_open")
+            opened.append(pp.value)
+            if bq_ == bp:
+                pq = pp
+            else:
+                check(lib.bq_ipc_open(bq_, C.byref(pq)), "bq_ipc_open")
+                opened.append(pq.value)
+            aP[r], aQ[r] = pp.value + op, pq.value + oq
+        check(lib.bq_ctx_set_scan_peers(self.ctx.handle, aP, aQ), "bq_ctx_set_scan_peers")
+        self.dist.barrier(group=self.group)
+        return opened
+
+    def release_tables(self, opened):
+        self.dist.barrier(group=self.group)
+        for p in opened:
+            self.ctx.lib.bq_ipc_close(C.c_void_p(p))
+        self.ctx.lib.bq_ctx_set_scan_peers(self.ctx.handle, None, None)
+
+
+def dist_world():
+    """The DistWorld over the default process group (created on first use)."""
+    global _dist_world
+    if _dist_world is None:
+        _dist_world = DistWorld()
+    return _dist_world
+
+
+class CpuWorld:
+    """gloo ranks (or a single process) on the CPU backend."""
+
+    def __init__(self, group=None, threads=None):
+        self.lib, _ = _native.load()
+        self.group = group
+        self.threads = threads or max(1, (os.cpu_count() or 1))
+        try:
+            import torch.distributed as dist
+            self.dist = dist if dist.is_initialized() else None
+        except Exception:
+            self.dist = None
+        self.rank = self.dist.get_rank(group) if self.dist else 0
+        self.size = self.dist.get_world_size(group) if self.dist else 1
+
+    def integrate(self, job):
+        res = Result()
+        if self.size == 1:
+            check(self.lib.bq_cpu_integrate(C.byref(job), self.threads, C.byref(res)),
+                  "bq_cpu_integrate")
+            return res
+        import torch
+        check(self.lib.bq_cpu_integrate_segments(C.byref(job), self.rank, self.size,
+                                                 max(1, self.threads // self.size), C.byref(res)),
+              "bq_cpu_integrate_segments")
+        mine = torch.tensor([list(res.seg_hi), list(res.seg_lo)], dtype=torch.float64)
+        parts = [torch.zeros_like(mine) for _ in range(self.size)]
+        self.dist.all_gather(parts, mine, group=self.group)
+        segs = _native.SEGMENTS // self.size
+        hi = (C.c_double * _native.SEGMENTS)()
+        lo = (C.c_double * _native.SEGMENTS)()
+        for r, t in enumerate(parts):          # rank r owns segments [r*segs, (r+1)*segs)
+            for s in range(r * segs, (r + 1) * segs):
+                hi[s], lo[s] = float(t[0, s]), float(t[1, s])
+        out = Result()
+        check(self.lib.bq_fold_segments(C.byref(job), hi, lo, C.byref(out)), "bq_fold_segments")
+        out.world, out.rank = self.size, self.rank
+        return out

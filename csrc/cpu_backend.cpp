@@ -1,0 +1,235 @@
+// CPU backend: walks exactly the summation tree of the sm_100a kernel
+// (quad_kernel.cu) with std::thread workers, so a box without a GPU can run
+// the API, the CLIs and the tests.  It plays the role the MPI programs play in
+// the reference (riemann.cpp:47-101, 4main.c:42-247) but with every "rank"
+// being a chunk of the fixed tree instead of a slice that depends on -n.
+#include <math.h>
+#include <string.h>
+
+#include <atomic>
+#include <thread>
+#include <vector>
+
+#include "host_common.h"
+#include "quad_core.cuh"
+
+namespace bq {
+
+static inline void host_sincos(double x, double* s, double* c) { ::sincos(x, s, c); }
+
+// The 32-lane xor butterfly of warp_reduce_dd(); lane 0's value.
+static dd butterfly(dd* v, int lanes) {
+    dd tmp[32];
+    for (int off = lanes / 2; off >= 1; off >>= 1) {
+        for (int l = 0; l < lanes; ++l) tmp[l] = dd_add(v[l], v[l ^ off]);
+        for (int l = 0; l < lanes; ++l) v[l] = tmp[l];
+    }
+    return v[0];
+}
+
+template <class F, class R>
+struct CpuWorker {
+    const Plan& P;
+    F f;
+    bool rotate;
+    // column constants per virtual thread
+    std::vector<R> cj, sj;
+    std::vector<double> dx;
+
+    CpuWorker(const Plan& P_, const double* table)
+        : P(P_), f(make_functor<F>(P_, table)), rotate(P_.eval == BQ_EVAL_ROTATE) {
+        cj.resize(kThreads * kCols);
+        sj.resize(kThreads * kCols);
+        dx.resize(kThreads * kCols);
+        for (int t = 0; t < kThreads; ++t)
+            for (int j = 0; j < kCols; ++j) {
+                const double col = double(t + kThreads * j);
+                const int idx = t * kCols + j;
+                if (rotate) {
+                    dx[idx] = col * P.h;
+                    double s, c;
+                    host_sincos(f.angle(dx[idx]), &s, &c);
+                    cj[idx] = R(c);
+                    sj[idx] = R(s);
+                } else {
+                    dx[idx] = col;
+                    cj[idx] = R(0);
+                    sj[idx] = R(0);
+                }
+            }
+    }
+
+    dd part(uint32_t part_idx) const {
+        uint64_t lo, hi;
+        part_tiles(P, part_idx, lo, hi);
+        dd total[kThreads];
+        for (int t = 0; t < kThreads; ++t) total[t] = dd{0.0, 0.0};
+        R S[kMaxRows + 1], C[kMaxRows + 1];
+        double X0[kMaxRows + 1];
+        for (uint64_t tile = lo; tile < hi; ++tile) {
+            const TileGeom g = tile_geom(P, tile);
+            const uint32_t rows = g.full_rows + (g.rem ? 1u : 0u);
+            if (rotate) {
+                for (uint32_t k = 0; k < rows; ++k) {
+                    const double x0 = fma(row_base_index(P, g, k), P.h, P.a);
+                    double s, c;
+                    host_sincos(f.angle(x0), &s, &c);
+                    S[k] = R(s);
+                    C[k] = R(c);
+                    X0[k] = x0;
+                }
+            }
+            for (int t = 0; t < kThreads; ++t) {
+                const R* cjt = &cj[t * kCols];
+                const R* sjt = &sj[t * kCols];
+                const double* dxt = &dx[t * kCols];
+                TileAcc<R> acc;
+                acc.clear();
+                double rb = row_base_index(P, g, 0);
+                for (uint32_t r = 0; r < g.full_rows; ++r) {
+                    R v[kCols];
+                    for (int j = 0; j < kCols; ++j)
+                        v[j] = rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j], X0[r], dxt[j])
+                                      : point_direct<F, R>(f, rb, dxt[j], P.h, P.a);
+                    acc.add_row(v);
+                    rb += double(kWidth);
+                }
+                if (g.rem) {
+                    const uint32_t r = g.full_rows;
+                    for (int j = 0; j < kCols; ++j)
+                        if (uint32_t(t + kThreads * j) < g.rem)
+                            acc.add_one(j, rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j],
+                                                                       X0[r], dxt[j])
+                                                  : point_direct<F, R>(f, rb, dxt[j], P.h, P.a));
+                }
+                total[t] = dd_add_d(total[t], acc.flush());
+            }
+        }
+        // block_reduce_dd(): 8 warp butterflies, then an 8-lane butterfly.
+        dd wsum[8];
+        for (int w = 0; w < kThreads / 32; ++w) wsum[w] = butterfly(&total[w * 32], 32);
+        return butterfly(wsum, 8);
+    }
+
+    dd chunk(uint32_t c) const {
+        const dd p0 = part(c * kPartsPerChunk + 0);
+        const dd p1 = part(c * kPartsPerChunk + 1);
+        return dd_add(p0, p1);
+    }
+};
+
+static dd segment_sum(const dd* partials, uint32_t seg) {
+    dd lanes[32];
+    const uint32_t c0 = seg * kChunksPerSegment;
+    for (int l = 0; l < 32; ++l) {
+        dd acc{0.0, 0.0};
+        for (uint32_t c = c0 + l; c < c0 + kChunksPerSegment; c += 32) acc = dd_add(acc, partials[c]);
+        lanes[l] = acc;
+    }
+    return butterfly(lanes, 32);
+}
+
+template <class F, class R>
+static void run_segments(const Plan& P, const double* table, int threads, double* seg_hi,
+                         double* seg_lo) {
+    CpuWorker<F, R> worker(P, table);
+    std::vector<dd> partials(kChunks, dd{0.0, 0.0});
+    std::atomic<uint32_t> next(P.chunk_lo);
+    auto body = [&]() {
+        for (;;) {
+            const uint32_t c = next.fetch_add(1);
+            if (c >= P.chunk_hi) break;
+            partials[c] = worker.chunk(c);
+        }
+    };
+    if (threads <= 1) {
+        body();
+    } else {
+        std::vector<std::thread> pool;
+        for (int i = 0; i < threads; ++i) pool.emplace_back(body);
+        for (auto& th : pool) th.join();
+    }
+    for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s) {
+        const dd v = segment_sum(partials.data(), s);
+        seg_hi[s] = v.hi;
+        seg_lo[s] = v.lo;
+    }
+}
+
+template <class F>
+static void run_f(const Plan& P, const double* table, int threads, double* hi, double* lo) {
+    if (P.dtype == BQ_F64)
+        run_segments<F, double>(P, table, threads, hi, lo);
+    else
+        run_segments<F, float>(P, table, threads, hi, lo);
+}
+
+static int cpu_segments(const bq_job* job, int rank, int world, int threads, const double* table,
+                        int table_len, Plan* P, double* hi, double* lo) {
+    int table_default_len = 0;
+    if (!table) table = default_profile(&table_default_len), table_len = table_default_len;
+    const int rc = make_plan(*job, rank, world, 0, table_len, P);
+    if (rc != BQ_OK) return rc;
+    for (int s = 0; s < kSegments; ++s) hi[s] = lo[s] = 0.0;
+    switch (P->integrand) {
+        case BQ_F_SIN: run_f<SinF>(*P, table, threads, hi, lo); break;
+        case BQ_F_ACC: run_f<AccF>(*P, table, threads, hi, lo); break;
+        case BQ_F_VEL: run_f<VelF>(*P, table, threads, hi, lo); break;
+        case BQ_F_DIS: run_f<DisF>(*P, table, threads, hi, lo); break;
+        case BQ_F_PROFILE: run_f<ProfileF>(*P, table, threads, hi, lo); break;
+        default: return BQ_ERR_INVALID;
+    }
+    return BQ_OK;
+}
+
+int fold_segments(const Plan& P, const double* table, const double* hi, const double* lo,
+                  bq_result* out) {
+    switch (P.integrand) {
+        case BQ_F_SIN: finish_result(P, make_functor<SinF>(P, table), hi, lo, out); break;
+        case BQ_F_ACC: finish_result(P, make_functor<AccF>(P, table), hi, lo, out); break;
+        case BQ_F_VEL: finish_result(P, make_functor<VelF>(P, table), hi, lo, out); break;
+        case BQ_F_DIS: finish_result(P, make_functor<DisF>(P, table), hi, lo, out); break;
+        case BQ_F_PROFILE: finish_result(P, make_functor<ProfileF>(P, table), hi, lo, out); break;
+        default: return BQ_ERR_INVALID;
+    }
+    out->status = BQ_OK;
+    return BQ_OK;
+}
+
+}  // namespace bq
+
+extern "C" {
+
+int bq_cpu_integrate_segments(const bq_job* job, int rank, int world, int threads, bq_result* out) {
+    if (!job || !out) return BQ_ERR_INVALID;
+    memset(out, 0, sizeof(*out));
+    bq::Plan P;
+    return bq::cpu_segments(job, rank, world, threads, nullptr, 0, &P, out->seg_hi, out->seg_lo);
+}
+
+int bq_cpu_integrate(const bq_job* job, int threads, bq_result* out) {
+    if (!job || !out) return BQ_ERR_INVALID;
+    memset(out, 0, sizeof(*out));
+    bq::Plan P;
+    double hi[BQ_SEGMENTS], lo[BQ_SEGMENTS];
+    const int rc = bq::cpu_segments(job, 0, 1, threads, nullptr, 0, &P, hi, lo);
+    if (rc != BQ_OK) return rc;
+    int len = 0;
+    return bq::fold_segments(P, bq::default_profile(&len), hi, lo, out);
+}
+
+int bq_fold_segments(const bq_job* job, const double* seg_hi, const double* seg_lo, bq_result* out) {
+    if (!job || !out || !seg_hi || !seg_lo) return BQ_ERR_INVALID;
+    bq::Plan P;
+    int len = 0;
+    const double* table = bq::default_profile(&len);
+    const int rc = bq::make_plan(*job, 0, 1, 0, len, &P);
+    if (rc != BQ_OK) return rc;
+    double hi[BQ_SEGMENTS], lo[BQ_SEGMENTS];
+    memcpy(hi, seg_hi, sizeof(hi));
+    memcpy(lo, seg_lo, sizeof(lo));
+    memset(out, 0, sizeof(*out));
+    return bq::fold_segments(P, table, hi, lo, out);
+}
+
+}  // extern "C"

@@ -1,0 +1,281 @@
+// CPU backend of cumulative integration: the tile / segment tree of
+// scan_kernel.cu on host threads (capability of 4main.c:76-225).
+#include <math.h>
+#include <string.h>
+
+#include <atomic>
+#include <thread>
+#include <vector>
+
+#include "host_common.h"
+#include "quad_core.cuh"
+#include "scan_core.cuh"
+
+namespace bq {
+
+int make_scan_plan(const bq_scan_job& job, int rank, int world, int table_len, ScanPlan* P) {
+    memset(P, 0, sizeof(*P));
+    if (job.n < 1 || job.n > kScanMaxN) {
+        set_error("cumulative: n=%llu out of range [1, 2^34]", (unsigned long long)job.n);
+        return BQ_ERR_INVALID;
+    }
+    if (world < 1 || world > BQ_MAX_WORLD || (kSegments % world) != 0 || rank < 0 || rank >= world) {
+        set_error("world=%d rank=%d: world must be 1, 2, 4 or 8", world, rank);
+        return BQ_ERR_INVALID;
+    }
+    if (job.integrand < 0 || job.integrand >= BQ_F_COUNT || !isfinite(job.x0) || !isfinite(job.dx)) {
+        set_error("cumulative: bad integrand / grid");
+        return BQ_ERR_INVALID;
+    }
+    P->n = job.n;
+    P->x0 = job.x0;
+    P->dx = job.dx;
+    P->integrand = job.integrand;
+    for (int i = 0; i < 4; ++i) P->p[i] = job.p[i];
+    if (job.integrand == BQ_F_ACC || job.integrand == BQ_F_VEL || job.integrand == BQ_F_DIS) {
+        if (P->p[0] == 0.0) P->p[0] = kTscale;
+        if (P->p[1] == 0.0) P->p[1] = kAscale;
+        if (P->p[2] == 0.0) P->p[2] = kVscale;
+    }
+    if (job.integrand == BQ_F_PROFILE) {
+        if (P->p[0] == 0.0) P->p[0] = 1.0;
+        if (table_len < 2 || table_len > kMaxTable) {
+            set_error("PROFILE table length %d out of range", table_len);
+            return BQ_ERR_INVALID;
+        }
+        P->table_len = uint32_t(table_len);
+        const double xlast = job.x0 + double(job.n - 1) * job.dx;
+        const double lo = job.x0 < xlast ? job.x0 : xlast, hi = job.x0 < xlast ? xlast : job.x0;
+        const double xmax = double(table_len - 1) * P->p[0];
+        if (lo < 0.0 || hi > xmax * (1.0 + 1e-15)) {
+            set_error("PROFILE integrand is defined on [0, %g], grid spans [%g, %g]", xmax, lo, hi);
+            return BQ_ERR_RANGE;
+        }
+    }
+    P->rank = rank;
+    P->world = world;
+    P->flags = (job.replicate ? kScanReplicate : 0u) | (job.want_samples ? kScanSamples : 0u);
+    P->timeout_ms = 2000;
+    P->n_tiles = (job.n + kScanTile - 1) / kScanTile;
+    for (int s = 0; s <= kSegments; ++s) P->seg_tile[s] = (uint64_t(s) * P->n_tiles) / kSegments;
+    const uint32_t segs = kSegments / world;
+    P->seg_lo = rank * segs;
+    P->seg_hi = P->seg_lo + segs;
+    P->tile_lo = P->seg_tile[P->seg_lo];
+    P->tile_hi = P->seg_tile[P->seg_hi];
+    return BQ_OK;
+}
+
+namespace {
+
+// Kogge-Stone inclusive scan over 32 "lanes", as the kernel's shuffle loops do.
+template <class T, class Op>
+void lanes_inclusive(T* x, Op op) {
+    for (int d = 1; d < 32; d <<= 1) {
+        T tmp[32];
+        for (int l = 0; l < 32; ++l) tmp[l] = l >= d ? op(x[l - d], x[l], d) : x[l];
+        for (int l = 0; l < 32; ++l) x[l] = tmp[l];
+    }
+}
+
+double lanes_sum(const double* v, int lanes) {
+    double x[32], t[32];
+    for (int l = 0; l < lanes; ++l) x[l] = v[l];
+    for (int off = lanes / 2; off >= 1; off >>= 1) {
+        for (int l = 0; l < lanes; ++l) t[l] = x[l] + x[l ^ off];
+        for (int l = 0; l < lanes; ++l) x[l] = t[l];
+    }
+    return x[0];
+}
+
+template <class F>
+struct CpuScan {
+    const ScanPlan& P;
+    F f;
+    std::vector<double> agg, prefix;     // global tile indexing
+    Run seg_tot[kSegments];
+    Run seg_base[kSegments];
+
+    CpuScan(const ScanPlan& P_, const double* table) : P(P_) {
+        Plan fp;
+        memset(&fp, 0, sizeof(fp));
+        for (int i = 0; i < 4; ++i) fp.p[i] = P.p[i];
+        fp.table_len = P.table_len;
+        f = make_functor<F>(fp, table);
+        agg.assign(2 * P.n_tiles, 0.0);
+        prefix.assign(4 * P.n_tiles, 0.0);
+    }
+
+    void tile_aggregate(uint64_t tile) {
+        const uint32_t m = scan_tile_count(P, tile);
+        double ws[kScanThreads / 32], ww[kScanThreads / 32];
+        for (int w = 0; w < kScanThreads / 32; ++w) {
+            double ls[32], lw[32];
+            for (int l = 0; l < 32; ++l) {
+                const uint32_t k0 = uint32_t(w * 32 + l) * kScanItems;
+                double v[kScanItems];
+                scan_thread_values(f, P, tile * uint64_t(kScanTile) + k0, k0, m, v);
+                scan_thread_aggregate(v, k0, m, ls[l], lw[l]);
+            }
+            ws[w] = lanes_sum(ls, 32);
+            ww[w] = lanes_sum(lw, 32);
+        }
+        agg[2 * tile] = lanes_sum(ws, 8);
+        agg[2 * tile + 1] = lanes_sum(ww, 8);
+    }
+
+    Run tile_run(uint64_t t) const {
+        return run_from_tile(agg[2 * t], agg[2 * t + 1], double(scan_tile_count(P, t)));
+    }
+
+    void segment_prefixes(int seg) {
+        const uint64_t t0 = P.seg_tile[seg], t1 = P.seg_tile[seg + 1];
+        const uint64_t T = t1 - t0;
+        const uint64_t B = (T + kScanThreads - 1) / kScanThreads;
+        Run mine[kScanThreads];
+        uint64_t lo[kScanThreads], hi[kScanThreads];
+        for (int t = 0; t < kScanThreads; ++t) {
+            lo[t] = t0 + uint64_t(t) * B < t1 ? t0 + uint64_t(t) * B : t1;
+            hi[t] = lo[t] + B < t1 ? lo[t] + B : t1;
+            Run r = run_identity();
+            for (uint64_t i = lo[t]; i < hi[t]; ++i) r = run_combine(r, tile_run(i));
+            mine[t] = r;
+        }
+        Run inc[kScanThreads], warp_tot[kScanThreads / 32];
+        for (int w = 0; w < kScanThreads / 32; ++w) {
+            Run x[32];
+            for (int l = 0; l < 32; ++l) x[l] = mine[w * 32 + l];
+            lanes_inclusive(x, [](const Run& a, const Run& b, int) { return run_combine(a, b); });
+            for (int l = 0; l < 32; ++l) inc[w * 32 + l] = x[l];
+            warp_tot[w] = x[31];
+        }
+        Run last = run_identity();
+        for (int t = 0; t < kScanThreads; ++t) {
+            const int w = t >> 5, l = t & 31;
+            Run excl = l ? inc[t - 1] : run_identity();
+            Run wpre = run_identity();
+            for (int k = 0; k < w; ++k) wpre = run_combine(wpre, warp_tot[k]);
+            Run running = run_combine(wpre, excl);
+            for (uint64_t i = lo[t]; i < hi[t]; ++i) {
+                double* o = &prefix[4 * i];
+                o[0] = running.p.hi, o[1] = running.p.lo, o[2] = running.q.hi, o[3] = running.q.lo;
+                running = run_combine(running, tile_run(i));
+            }
+            if (t == kScanThreads - 1) last = running;
+        }
+        seg_tot[seg] = last;
+    }
+
+    void bases() {
+        Run base = run_identity();
+        for (int s = 0; s < kSegments; ++s) {
+            seg_base[s] = base;
+            Run t = seg_tot[s];
+            const uint64_t first = P.seg_tile[s] * uint64_t(kScanTile);
+            uint64_t last = P.seg_tile[s + 1] * uint64_t(kScanTile);
+            if (last > P.n) last = P.n;
+            t.cnt = double(last - first);
+            base = run_combine(base, t);
+        }
+    }
+
+    void tile_store(uint64_t tile, double* Pout, double* Qout, double* Sout) const {
+        const uint32_t m = scan_tile_count(P, tile);
+        const int seg = scan_segment_of(P, tile);
+        const double* p = &prefix[4 * tile];
+        Run pre{dd{p[0], p[1]}, dd{p[2], p[3]}, double((tile - P.seg_tile[seg]) * uint64_t(kScanTile))};
+        const Run2 tile_excl = scan_tile_exclusive(seg_base[seg], pre);
+        static thread_local double LP[kScanThreads][kScanItems], LQ[kScanThreads][kScanItems],
+            V[kScanThreads][kScanItems];
+        Run2 inc[kScanThreads], warp_tot[kScanThreads / 32];
+        for (int w = 0; w < kScanThreads / 32; ++w) {
+            Run2 x[32];
+            for (int l = 0; l < 32; ++l) {
+                const int t = w * 32 + l;
+                const uint32_t k0 = uint32_t(t) * kScanItems;
+                scan_thread_values(f, P, tile * uint64_t(kScanTile) + k0, k0, m, V[t]);
+                scan_thread_local(V[t], LP[t], LQ[t]);
+                x[l] = Run2{LP[t][kScanItems - 1], LQ[t][kScanItems - 1]};
+            }
+            lanes_inclusive(x, [](const Run2& a, const Run2& b, int d) {
+                return run2_combine(a, b, double(kScanItems * d));
+            });
+            for (int l = 0; l < 32; ++l) inc[w * 32 + l] = x[l];
+            warp_tot[w] = x[31];
+        }
+        for (int t = 0; t < kScanThreads; ++t) {
+            const int w = t >> 5, l = t & 31;
+            const uint32_t k0 = uint32_t(t) * kScanItems;
+            Run2 excl = l ? inc[t - 1] : Run2{0.0, 0.0};
+            Run2 wpre{0.0, 0.0};
+            for (int k = 0; k < w; ++k) wpre = run2_combine(wpre, warp_tot[k], double(32 * kScanItems));
+            const Run2 et = run2_combine(wpre, excl, double(kScanItems * l));
+            const Run2 full = run2_combine(tile_excl, et, double(k0));
+            for (int j = 0; j < kScanItems; ++j) {
+                if (k0 + j >= m) break;
+                const uint64_t i = tile * uint64_t(kScanTile) + k0 + j;
+                Pout[i] = full.p + LP[t][j];
+                Qout[i] = fma(double(j + 1), full.p, full.q) + LQ[t][j];
+                if (Sout) Sout[i] = V[t][j];
+            }
+        }
+    }
+};
+
+template <class F>
+int run_scan(const ScanPlan& P, const double* table, int threads, double* Pout, double* Qout,
+             double* Sout, bq_scan_result* out) {
+    CpuScan<F> S(P, table);
+    auto parallel_tiles = [&](auto fn) {
+        std::atomic<uint64_t> next(0);
+        auto body = [&]() {
+            for (;;) {
+                const uint64_t t = next.fetch_add(1);
+                if (t >= P.n_tiles) break;
+                fn(t);
+            }
+        };
+        if (threads <= 1) {
+            body();
+        } else {
+            std::vector<std::thread> pool;
+            for (int i = 0; i < threads; ++i) pool.emplace_back(body);
+            for (auto& th : pool) th.join();
+        }
+    };
+    parallel_tiles([&](uint64_t t) { S.tile_aggregate(t); });
+    for (int s = 0; s < kSegments; ++s) S.segment_prefixes(s);
+    S.bases();
+    parallel_tiles([&](uint64_t t) { S.tile_store(t, Pout, Qout, Sout); });
+    memset(out, 0, sizeof(*out));
+    out->p_last = Pout[P.n - 1];
+    out->q_last = Qout[P.n - 1];
+    out->p_second_last = P.n >= 2 ? Pout[P.n - 2] : 0.0;
+    out->slice_begin = 0;
+    out->slice_end = P.n;
+    out->world = 1;
+    out->status = BQ_OK;
+    return BQ_OK;
+}
+
+}  // namespace
+}  // namespace bq
+
+extern "C" int bq_cpu_cumulative(const bq_scan_job* job, int threads, double* P, double* Q,
+                                 double* samples, bq_scan_result* out) {
+    using namespace bq;
+    if (!job || !P || !Q || !out) return BQ_ERR_INVALID;
+    int len = 0;
+    const double* table = default_profile(&len);
+    ScanPlan plan;
+    const int rc = make_scan_plan(*job, 0, 1, len, &plan);
+    if (rc != BQ_OK) return rc;
+    switch (plan.integrand) {
+        case BQ_F_SIN: return run_scan<SinF>(plan, table, threads, P, Q, samples, out);
+        case BQ_F_ACC: return run_scan<AccF>(plan, table, threads, P, Q, samples, out);
+        case BQ_F_VEL: return run_scan<VelF>(plan, table, threads, P, Q, samples, out);
+        case BQ_F_DIS: return run_scan<DisF>(plan, table, threads, P, Q, samples, out);
+        case BQ_F_PROFILE: return run_scan<ProfileF>(plan, table, threads, P, Q, samples, out);
+        default: return BQ_ERR_INVALID;
+    }
+}

@@ -1,0 +1,454 @@
+// CUDA host runtime: contexts, pinned staging, peer wiring, launches.
+//
+// The reference's host side is three main()s that cudaMalloc/cudaMemcpy 144 MB
+// of uninitialised memory per run and never check an error
+// (cintegrate.cu:111-133).  Here one context per device owns every buffer for
+// its lifetime; a call moves sizeof(Plan) bytes down and sizeof(bq_result)
+// bytes up, both through pinned memory, around exactly one kernel launch.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "ctx.h"
+#include "host_common.h"
+#include "quad_launch.h"
+#include "scan_launch.h"
+
+namespace bq {
+
+#define BQ_CUDA(expr)                                                                      \
+    do {                                                                                   \
+        cudaError_t e_ = (expr);                                                           \
+        if (e_ != cudaSuccess) {                                                           \
+            set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__,    \
+                      __LINE__);                                                           \
+            return BQ_ERR_CUDA;                                                            \
+        }                                                                                  \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+}  // namespace bq
+
+using namespace bq;
+
+extern "C" {
+
+int bq_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int bq_ctx_create(int device, bq_ctx** out) {
+    if (!out) return BQ_ERR_INVALID;
+    *out = nullptr;
+    int ndev = bq_cuda_device_count();
+    if (device < 0 || device >= ndev) {
+        set_error("device %d not available (%d CUDA devices)", device, ndev);
+        return BQ_ERR_INVALID;
+    }
+    DeviceGuard guard(device);
+    bq_ctx* c = new bq_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    BQ_CUDA(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    c->cc_major = prop.major;
+    BQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    BQ_CUDA(cudaEventCreate(&c->ev0));
+    BQ_CUDA(cudaEventCreate(&c->ev1));
+
+    BQ_CUDA(cudaMalloc(&c->d_plans, sizeof(PlanSlot) * kRing));
+    BQ_CUDA(cudaMalloc(&c->d_partials, sizeof(dd) * kChunks));
+    BQ_CUDA(cudaMemset(c->d_partials, 0, sizeof(dd) * kChunks));
+    BQ_CUDA(cudaMalloc(&c->d_ticket, 256));
+    BQ_CUDA(cudaMemset(c->d_ticket, 0, 256));
+    BQ_CUDA(cudaMalloc(&c->d_result, sizeof(bq_result)));
+    BQ_CUDA(cudaMemset(c->d_result, 0, sizeof(bq_result)));
+    BQ_CUDA(cudaMalloc(&c->d_scan_result, sizeof(bq_scan_result)));
+    BQ_CUDA(cudaMemset(c->d_scan_result, 0, sizeof(bq_scan_result)));
+    BQ_CUDA(cudaMalloc(&c->d_comm, sizeof(CommBlock)));
+    BQ_CUDA(cudaMemset(c->d_comm, 0, sizeof(CommBlock)));
+    BQ_CUDA(cudaMalloc(&c->d_table, sizeof(double) * (kMaxTable + 2)));
+    BQ_CUDA(cudaMemset(c->d_table, 0, sizeof(double) * (kMaxTable + 2)));
+    BQ_CUDA(cudaMalloc(&c->d_seg_scratch, sizeof(double) * 2 * kSegments));
+
+    BQ_CUDA(cudaHostAlloc(&c->h_plans, sizeof(PlanSlot) * kRing, cudaHostAllocDefault));
+    BQ_CUDA(cudaHostAlloc(&c->h_result, sizeof(bq_result), cudaHostAllocDefault));
+    BQ_CUDA(cudaHostAlloc(&c->h_scan_result, sizeof(bq_scan_result), cudaHostAllocDefault));
+    memset(c->h_result, 0, sizeof(bq_result));
+    memset(c->h_scan_result, 0, sizeof(bq_scan_result));
+    for (int i = 0; i < kRing; ++i) {
+        BQ_CUDA(cudaEventCreateWithFlags(&c->ring_ev[i], cudaEventDisableTiming));
+        c->ring_busy[i] = false;
+    }
+    for (int r = 0; r < BQ_MAX_WORLD; ++r) c->peers[r] = nullptr, c->peer_ipc[r] = false;
+    c->peers[0] = c->d_comm;
+
+    int len = 0;
+    const double* t = default_profile(&len);
+    int rc = bq_ctx_set_profile(c, t, len);
+    if (rc != BQ_OK) return rc;
+    rc = scan_ctx_init(c);
+    if (rc != BQ_OK) return rc;
+    BQ_CUDA(cudaDeviceSynchronize());
+    *out = c;
+    return BQ_OK;
+}
+
+void bq_ctx_destroy(bq_ctx* c) {
+    if (!c) return;
+    DeviceGuard guard(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (int r = 0; r < BQ_MAX_WORLD; ++r)
+        if (c->peer_ipc[r] && c->peers[r]) cudaIpcCloseMemHandle(c->peers[r]);
+    scan_ctx_free(c);
+    cudaFree(c->d_plans);
+    cudaFree(c->d_partials);
+    cudaFree(c->d_ticket);
+    cudaFree(c->d_result);
+    cudaFree(c->d_scan_result);
+    cudaFree(c->d_comm);
+    cudaFree(c->d_table);
+    cudaFree(c->d_seg_scratch);
+    cudaFreeHost(c->h_plans);
+    cudaFreeHost(c->h_result);
+    cudaFreeHost(c->h_scan_result);
+    for (int i = 0; i < kRing; ++i) cudaEventDestroy(c->ring_ev[i]);
+    cudaEventDestroy(c->ev0);
+    cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int bq_ctx_device(const bq_ctx* c) { return c ? c->device : -1; }
+void* bq_ctx_stream(const bq_ctx* c) { return c ? (void*)c->stream : nullptr; }
+const bq_result* bq_ctx_device_result(const bq_ctx* c) { return c ? c->d_result : nullptr; }
+
+int bq_ctx_set_profile(bq_ctx* c, const double* table, int len) {
+    if (!c || !table || len < 2 || len > kMaxTable) {
+        set_error("profile table length %d out of range [2, %d]", len, kMaxTable);
+        return BQ_ERR_INVALID;
+    }
+    DeviceGuard guard(c->device);
+    std::vector<double> padded(size_t(len) + 2, 0.0);
+    memcpy(padded.data(), table, sizeof(double) * len);
+    padded[len] = table[len - 1];   // pad so the bulk copy size is a multiple of 16 bytes
+    BQ_CUDA(cudaStreamSynchronize(c->stream));
+    BQ_CUDA(cudaMemcpy(c->d_table, padded.data(), sizeof(double) * (len + 2), cudaMemcpyHostToDevice));
+    c->table_len = len;
+    c->h_table.assign(table, table + len);
+    return BQ_OK;
+}
+
+int bq_ctx_configure(bq_ctx* c, int ctas_per_sm, int cluster, int rows_per_tile) {
+    if (!c) return BQ_ERR_INVALID;
+    if (ctas_per_sm < 0 || ctas_per_sm > 8 || (cluster != 0 && cluster != 1 && cluster != 2) ||
+        rows_per_tile < 0 || rows_per_tile > kMaxRows) {
+        set_error("bad launch configuration");
+        return BQ_ERR_INVALID;
+    }
+    c->ctas_per_sm = ctas_per_sm ? ctas_per_sm : 2;
+    c->cluster = cluster ? cluster : 2;
+    c->rows_override = uint32_t(rows_per_tile);
+    return BQ_OK;
+}
+
+int bq_ctx_set_timeout_ms(bq_ctx* c, int ms) {
+    if (!c || ms < 1) return BQ_ERR_INVALID;
+    c->timeout_ms = uint32_t(ms);
+    return BQ_OK;
+}
+
+int bq_ctx_inject_fault(bq_ctx* c, int kind) {
+    if (!c) return BQ_ERR_INVALID;
+    c->fault_flags = kind ? kFlagSkipPublish : 0u;
+    return BQ_OK;
+}
+
+}  // extern "C"
+
+namespace bq {
+
+// Claims the next staging slot (waiting for its previous use to drain).
+int ring_acquire(bq_ctx* c, int* slot) {
+    const int s = c->ring_head;
+    c->ring_head = (c->ring_head + 1) % kRing;
+    if (c->ring_busy[s]) {
+        BQ_CUDA(cudaEventSynchronize(c->ring_ev[s]));
+        c->ring_busy[s] = false;
+    }
+    *slot = s;
+    return BQ_OK;
+}
+
+int ring_release(bq_ctx* c, int slot, cudaStream_t stream) {
+    BQ_CUDA(cudaEventRecord(c->ring_ev[slot], stream));
+    c->ring_busy[slot] = true;
+    return BQ_OK;
+}
+
+static LaunchConfig quad_config(const bq_ctx* c) {
+    LaunchConfig cfg;
+    cfg.cluster = unsigned(c->cluster);
+    unsigned grid = unsigned(c->sm_count * c->ctas_per_sm);
+    grid -= grid % cfg.cluster;
+    if (grid < cfg.cluster) grid = cfg.cluster;
+    cfg.grid = grid;
+    return cfg;
+}
+
+static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint32_t extra_flags,
+                        double* seg_out, cudaStream_t stream) {
+    int slot = 0;
+    int rc = ring_acquire(c, &slot);
+    if (rc != BQ_OK) return rc;
+    Plan* hp = &c->h_plans[slot].quad;
+    rc = make_plan(*job, rank, world, c->rows_override, c->table_len, hp);
+    if (rc != BQ_OK) return rc;
+    hp->flags = extra_flags | c->fault_flags;
+    c->fault_flags = 0;
+    hp->timeout_ms = c->timeout_ms;
+    if (world > 1 && !(hp->flags & kFlagLocalOnly)) {
+        for (int r = 0; r < world; ++r)
+            if (!c->peers[r]) {
+                set_error("rank %d: peer %d is not attached (world=%d)", rank, r, world);
+                return BQ_ERR_INVALID;
+            }
+    }
+    Plan* dp = &c->d_plans[slot].quad;
+    BQ_CUDA(cudaMemcpyAsync(dp, hp, sizeof(Plan), cudaMemcpyHostToDevice, stream));
+
+    DeviceState st;
+    memset(&st, 0, sizeof(st));
+    st.plan = dp;
+    st.partials = c->d_partials;
+    st.ticket = c->d_ticket;
+    st.result = c->d_result;
+    st.comm = c->d_comm;
+    for (int r = 0; r < BQ_MAX_WORLD; ++r) st.peers[r] = c->peers[r];
+    st.peers[rank] = c->d_comm;
+    st.table = c->d_table;
+    st.seg_out = seg_out;
+    BQ_CUDA(launch_quad(*hp, st, quad_config(c), stream));
+    c->launches += 1;
+    BQ_CUDA(cudaMemcpyAsync(c->h_result, c->d_result, sizeof(bq_result), cudaMemcpyDeviceToHost,
+                            stream));
+    c->last_stream = stream;
+    return ring_release(c, slot, stream);
+}
+
+}  // namespace bq
+
+extern "C" {
+
+int bq_integrate_async(bq_ctx* c, const bq_job* job, void* stream) {
+    if (!c || !job) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    return quad_enqueue(c, job, c->rank, c->world, 0, nullptr, s);
+}
+
+int bq_integrate_local_async(bq_ctx* c, const bq_job* job, int rank, int world, double* dSegPairs,
+                             void* stream) {
+    if (!c || !job) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    return quad_enqueue(c, job, rank, world, kFlagLocalOnly, dSegPairs, s);
+}
+
+int bq_result_fetch(bq_ctx* c, bq_result* out) {
+    if (!c || !out) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    BQ_CUDA(cudaStreamSynchronize(c->last_stream ? c->last_stream : c->stream));
+    *out = *c->h_result;
+    return out->status;
+}
+
+int bq_integrate(bq_ctx* c, const bq_job* job, bq_result* out) {
+    if (!c || !job || !out) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    BQ_CUDA(cudaEventRecord(c->ev0, c->stream));
+    int rc = quad_enqueue(c, job, c->rank, c->world, 0, nullptr, c->stream);
+    if (rc != BQ_OK) return rc;
+    BQ_CUDA(cudaEventRecord(c->ev1, c->stream));
+    BQ_CUDA(cudaStreamSynchronize(c->stream));
+    *out = *c->h_result;
+    float ms = 0.f;
+    BQ_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    out->device_ms = ms;
+    if (out->status != BQ_OK) set_error("kernel reported status %d", out->status);
+    return out->status;
+}
+
+// ---- peers ---------------------------------------------------------------
+
+int bq_ipc_export(void* dptr, unsigned char handle[BQ_IPC_HANDLE_BYTES]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == BQ_IPC_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    BQ_CUDA(cudaIpcGetMemHandle(&h, dptr));
+    memcpy(handle, &h, sizeof(h));
+    return BQ_OK;
+}
+
+int bq_ipc_open(const unsigned char handle[BQ_IPC_HANDLE_BYTES], void** dptr) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    BQ_CUDA(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return BQ_OK;
+}
+
+int bq_ipc_close(void* dptr) {
+    BQ_CUDA(cudaIpcCloseMemHandle(dptr));
+    return BQ_OK;
+}
+
+int bq_ctx_export_comm(bq_ctx* c, unsigned char handle[BQ_IPC_HANDLE_BYTES]) {
+    if (!c) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    return bq_ipc_export(c->d_comm, handle);
+}
+
+int bq_ctx_attach_peers(bq_ctx* c, int rank, int world, const unsigned char* handles) {
+    if (!c || rank < 0 || rank >= world || world > BQ_MAX_WORLD || (kSegments % world) != 0) {
+        set_error("attach_peers: bad rank/world %d/%d", rank, world);
+        return BQ_ERR_INVALID;
+    }
+    DeviceGuard guard(c->device);
+    for (int r = 0; r < BQ_MAX_WORLD; ++r) {
+        if (c->peer_ipc[r] && c->peers[r]) cudaIpcCloseMemHandle(c->peers[r]);
+        c->peers[r] = nullptr;
+        c->peer_ipc[r] = false;
+    }
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) {
+            c->peers[r] = c->d_comm;
+            continue;
+        }
+        if (!handles) return BQ_ERR_INVALID;
+        void* p = nullptr;
+        int rc = bq_ipc_open(handles + size_t(r) * BQ_IPC_HANDLE_BYTES, &p);
+        if (rc != BQ_OK) return rc;
+        c->peers[r] = (CommBlock*)p;
+        c->peer_ipc[r] = true;
+    }
+    c->rank = rank;
+    c->world = world;
+    return BQ_OK;
+}
+
+int bq_ctx_reset_comm(bq_ctx* c) {
+    if (!c) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    BQ_CUDA(cudaStreamSynchronize(c->stream));
+    BQ_CUDA(cudaMemset(c->d_comm, 0, sizeof(CommBlock)));
+    BQ_CUDA(cudaMemset(c->d_ticket, 0, 256));
+    BQ_CUDA(cudaDeviceSynchronize());
+    return BQ_OK;
+}
+
+// ---- single-process world ----------------------------------------------------
+
+struct bq_world {
+    std::vector<bq_ctx*> ctx;
+};
+
+int bq_world_create(int ndev, const int* devices, bq_world** out) {
+    if (!out || ndev < 1 || ndev > BQ_MAX_WORLD || (kSegments % ndev) != 0) {
+        set_error("world size %d must be 1, 2, 4 or 8", ndev);
+        return BQ_ERR_INVALID;
+    }
+    bq_world* w = new bq_world();
+    for (int r = 0; r < ndev; ++r) {
+        bq_ctx* c = nullptr;
+        int rc = bq_ctx_create(devices ? devices[r] : r, &c);
+        if (rc != BQ_OK) {
+            bq_world_destroy(w);
+            return rc;
+        }
+        w->ctx.push_back(c);
+    }
+    for (int r = 0; r < ndev; ++r) {
+        bq_ctx* c = w->ctx[r];
+        DeviceGuard guard(c->device);
+        for (int q = 0; q < ndev; ++q) {
+            if (q != r && w->ctx[q]->device != c->device) {
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, c->device, w->ctx[q]->device);
+                if (!can) {
+                    set_error("device %d cannot access device %d", c->device, w->ctx[q]->device);
+                    bq_world_destroy(w);
+                    return BQ_ERR_UNSUPPORTED;
+                }
+                cudaError_t e = cudaDeviceEnablePeerAccess(w->ctx[q]->device, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+                    set_error("cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+                    bq_world_destroy(w);
+                    return BQ_ERR_CUDA;
+                }
+                cudaGetLastError();
+            }
+            c->peers[q] = w->ctx[q]->d_comm;
+        }
+        c->rank = r;
+        c->world = ndev;
+    }
+    *out = w;
+    return BQ_OK;
+}
+
+void bq_world_destroy(bq_world* w) {
+    if (!w) return;
+    for (bq_ctx* c : w->ctx) bq_ctx_destroy(c);
+    delete w;
+}
+
+int bq_world_size(const bq_world* w) { return w ? int(w->ctx.size()) : 0; }
+bq_ctx* bq_world_ctx(bq_world* w, int rank) {
+    return (w && rank >= 0 && rank < int(w->ctx.size())) ? w->ctx[rank] : nullptr;
+}
+
+int bq_world_integrate(bq_world* w, const bq_job* job, bq_result* out) {
+    if (!w || !job) return BQ_ERR_INVALID;
+    const int n = int(w->ctx.size());
+    // Enqueue everywhere first: the kernels meet at the in-kernel barrier, so
+    // no rank may be waited for before all have been launched.
+    for (int r = 0; r < n; ++r) {
+        bq_ctx* c = w->ctx[r];
+        DeviceGuard guard(c->device);
+        BQ_CUDA(cudaEventRecord(c->ev0, c->stream));
+        int rc = quad_enqueue(c, job, r, n, 0, nullptr, c->stream);
+        if (rc != BQ_OK) return rc;
+        BQ_CUDA(cudaEventRecord(c->ev1, c->stream));
+    }
+    int worst = BQ_OK;
+    for (int r = 0; r < n; ++r) {
+        bq_ctx* c = w->ctx[r];
+        DeviceGuard guard(c->device);
+        BQ_CUDA(cudaStreamSynchronize(c->stream));
+        float ms = 0.f;
+        BQ_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        c->h_result->device_ms = ms;
+        if (out) out[r] = *c->h_result;
+        if (c->h_result->status != BQ_OK) worst = c->h_result->status;
+    }
+    return worst;
+}
+
+}  // extern "C"

@@ -1,0 +1,82 @@
+// Definition of the opaque bq_ctx (one per process x device).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <vector>
+
+#include "device_state.h"
+#include "plan.h"
+#include "scan_plan.h"
+
+namespace bq {
+
+constexpr int kRing = 64;   // pinned / device parameter slots in flight
+
+union PlanSlot {
+    Plan quad;
+    ScanPlan scan;
+    unsigned char raw[512];
+};
+static_assert(sizeof(Plan) <= 512 && sizeof(ScanPlan) <= 512, "PlanSlot too small");
+
+int ring_acquire(struct ::bq_ctx* c, int* slot);
+int ring_release(struct ::bq_ctx* c, int slot, cudaStream_t stream);
+
+}  // namespace bq
+
+struct bq_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int cc_major = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t last_stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    // launch knobs
+    int ctas_per_sm = 2;
+    int cluster = 2;
+    uint32_t rows_override = 0;
+    uint32_t timeout_ms = 2000;
+    uint32_t fault_flags = 0;
+
+    // device buffers (allocated once)
+    bq::PlanSlot* d_plans = nullptr;
+    bq::dd* d_partials = nullptr;
+    unsigned int* d_ticket = nullptr;     // [0] quad, [8] scan phase A, [16] scan phase B
+    bq_result* d_result = nullptr;
+    bq_scan_result* d_scan_result = nullptr;
+    bq::CommBlock* d_comm = nullptr;
+    double* d_table = nullptr;
+    double* d_seg_scratch = nullptr;
+    int table_len = 0;
+    std::vector<double> h_table;
+
+    // scan scratch (grown on demand, outside the timed path)
+    double* d_scan_agg = nullptr;         // [tiles][2]
+    double* d_scan_prefix = nullptr;      // [tiles][4]
+    double* d_scan_misc = nullptr;        // segment bases, ready flags
+    uint64_t scan_tiles_cap = 0;
+    double* scan_peerP[BQ_MAX_WORLD] = {};
+    double* scan_peerQ[BQ_MAX_WORLD] = {};
+    int scan_grid = 0;
+
+    // pinned staging
+    bq::PlanSlot* h_plans = nullptr;
+    bq_result* h_result = nullptr;
+    bq_scan_result* h_scan_result = nullptr;
+    cudaEvent_t ring_ev[bq::kRing];
+    bool ring_busy[bq::kRing];
+    int ring_head = 0;
+
+    // world
+    int rank = 0, world = 1;
+    bq::CommBlock* peers[BQ_MAX_WORLD];
+    bool peer_ipc[BQ_MAX_WORLD];
+
+    uint64_t launches = 0;
+};
+
+namespace bq {
+int scan_ctx_init(bq_ctx* c);
+void scan_ctx_free(bq_ctx* c);
+}  // namespace bq

@@ -1,0 +1,14 @@
+// Host-only helpers shared by the CUDA runtime, the CPU backend and the CLIs.
+#pragma once
+#include <stdint.h>
+
+#include "plan.h"
+
+namespace bq {
+
+const double* default_profile(int* len);
+void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
+const char* last_error();
+long double oracle_sin_sum(double a, double b, uint64_t n, int rule);
+
+}  // namespace bq

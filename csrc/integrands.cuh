@@ -1,0 +1,92 @@
+// Integrand library (host + device functors).
+//
+//  SinF      sin(x)                         riemann.cpp:37, cintegrate.cu:68
+//  AccF      -sin(x/tscale)*ascale          riemann.cpp:103-106
+//  VelF      (1-cos(x/tscale))*vscale       riemann.cpp:108-111
+//  DisF      vscale*(x-tscale*sin(x/tscale)) riemann.cpp:113-116
+//  ProfileF  lerp of a uniform table        4main.c:249-269, cintegrate.cu:23-44
+//
+// Each functor offers
+//   eval(x)            - plain evaluation (DIRECT mode; any x)
+//   angle(x)           - for trig functors, the argument of sin/cos
+//   eval_sc(x, s, c)   - evaluation given s=sin(angle(x)), c=cos(angle(x))
+//                        (ROTATE mode: the kernel supplies s/c by rotation)
+// templated on the real type so the compensated-fp32 path shares them.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#include "bq_dd.cuh"
+
+namespace bq {
+
+BQ_HD double bq_sin(double x) { return sin(x); }
+BQ_HD double bq_cos(double x) { return cos(x); }
+BQ_HD float bq_sin(float x) { return sinf(x); }
+BQ_HD float bq_cos(float x) { return cosf(x); }
+
+struct SinF {
+    static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = false;
+    template <class R>
+    BQ_HD R eval(R x) const { return bq_sin(x); }
+    BQ_HD double angle(double x) const { return x; }
+    template <class R>
+    BQ_HD R eval_sc(R, R s, R) const { return s; }
+};
+
+struct AccF {
+    static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = false;
+    double tscale, ascale;
+    template <class R>
+    BQ_HD R eval(R x) const { return -(bq_sin(x / R(tscale)) * R(ascale)); }
+    BQ_HD double angle(double x) const { return x / tscale; }
+    template <class R>
+    BQ_HD R eval_sc(R, R s, R) const { return -(s * R(ascale)); }
+};
+
+struct VelF {
+    static constexpr bool kTrig = true, kNeedS = false, kNeedC = true, kNeedX = false;
+    double tscale, vscale;
+    template <class R>
+    BQ_HD R eval(R x) const { return (-bq_cos(x / R(tscale)) + R(1)) * R(vscale); }
+    BQ_HD double angle(double x) const { return x / tscale; }
+    template <class R>
+    BQ_HD R eval_sc(R, R, R c) const { return (-c + R(1)) * R(vscale); }
+};
+
+struct DisF {
+    static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = true;
+    double tscale, vscale;
+    template <class R>
+    BQ_HD R eval(R x) const { return R(vscale) * (x - (R(tscale) * bq_sin(x / R(tscale)))); }
+    BQ_HD double angle(double x) const { return x / tscale; }
+    template <class R>
+    BQ_HD R eval_sc(R x, R s, R) const { return R(vscale) * (x - (R(tscale) * s)); }
+};
+
+// Uniform-grid table, linear interpolation.  The reference reads
+// table[(int)t + 1] unconditionally (4main.c:264-268), which runs one past the
+// end at t == 1800; here the cell index is clamped to [0, len-2] so the closed
+// right end is valid, and anything outside [0, (len-1)*spacing] extrapolates
+// the edge cell linearly (the kernel flags it as BQ_ERR_RANGE).
+struct ProfileF {
+    static constexpr bool kTrig = false, kNeedS = false, kNeedC = false, kNeedX = true;
+    const double* table;
+    int len;
+    double inv_dx;
+    template <class R>
+    BQ_HD R eval(R x) const {
+        R u = x * R(inv_dx);
+        int i = (int)u;
+        i = i < 0 ? 0 : (i > len - 2 ? len - 2 : i);
+        R frac = u - R(i);
+        R t0 = R(table[i]);
+        R t1 = R(table[i + 1]);
+        return t0 + (t1 - t0) * frac;
+    }
+    BQ_HD double angle(double) const { return 0.0; }
+    template <class R>
+    BQ_HD R eval_sc(R x, R, R) const { return eval(x); }
+};
+
+}  // namespace bq

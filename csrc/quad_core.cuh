@@ -1,0 +1,160 @@
+// Per-point / per-thread arithmetic shared verbatim by the sm_100a kernel
+// (quad_kernel.cu) and by the CPU backend (cpu_backend.cpp), so both walk the
+// same summation tree.  Nothing here touches memory.
+#pragma once
+#include "bq_dd.cuh"
+#include "integrands.cuh"
+#include "plan.h"
+
+namespace bq {
+
+BQ_HD double bq_fma(double a, double b, double c) { return fma(a, b, c); }
+BQ_HD float bq_fma(float a, float b, float c) { return fmaf(a, b, c); }
+
+// ROTATE: f at angle(x0) + angle(dx) from the row base (S, C) = sincos(angle(x0))
+// and the column constants (cj, sj) = cos/sin(angle(dx)).  DMUL + DFMA per
+// needed component; for SinF that is the whole evaluation.
+template <class F, class R>
+BQ_HD R point_rotate(const F& f, R S, R C, R cj, R sj, double x0, double dx) {
+    R s = R(0), c = R(0);
+    if (F::kNeedS) s = bq_fma(C, sj, S * cj);
+    if (F::kNeedC) c = bq_fma(-S, sj, C * cj);
+    R x = F::kNeedX ? R(x0 + dx) : R(0);
+    return f.eval_sc(x, s, c);
+}
+
+// DIRECT: x = a + (i + off) * h with a single rounding (the index arithmetic
+// rowbase + col is exact in fp64 below 2^52), then a plain call of f.
+template <class F, class R>
+BQ_HD R point_direct(const F& f, double rowbase, double col, double h, double a) {
+    double x = fma(rowbase + col, h, a);
+    return f.template eval<R>(R(x));
+}
+
+// Per-thread, per-tile accumulator.
+//   fp64: kCols independent naive sums (<= kMaxRows terms each), combined
+//         pairwise and pushed into the thread's dd total at the end of a tile.
+//   fp32: the kCols values of a row are summed pairwise, the row sums are
+//         Kahan-accumulated in fp32, and the compensated value is promoted to
+//         fp64 at the end of a tile.
+template <class R>
+struct TileAcc;
+
+template <>
+struct TileAcc<double> {
+    double a[kCols];
+    BQ_HD void clear() {
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) a[j] = 0.0;
+    }
+    BQ_HD void add_row(const double (&v)[kCols]) {
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) a[j] += v[j];
+    }
+    BQ_HD void add_one(int j, double v) { a[j] += v; }
+    BQ_HD double flush() const {
+        double s = 0.0;
+        if (kCols == 4) {
+            s = (a[0] + a[1]) + (a[2] + a[3]);
+        } else {
+            for (int j = 0; j < kCols; ++j) s += a[j];
+        }
+        return s;
+    }
+};
+
+template <>
+struct TileAcc<float> {
+    float sum, comp;
+    BQ_HD void clear() { sum = 0.f, comp = 0.f; }
+    BQ_HD void add_row(const float (&v)[kCols]) {
+        float r;
+        if (kCols == 4) {
+            r = (v[0] + v[1]) + (v[2] + v[3]);
+        } else {
+            r = 0.f;
+            for (int j = 0; j < kCols; ++j) r += v[j];
+        }
+        kahan_add(sum, comp, r);
+    }
+    BQ_HD void add_one(int, float v) { kahan_add(sum, comp, v); }
+    BQ_HD double flush() const { return double(sum) - double(comp); }
+};
+
+// Geometry of one tile.
+struct TileGeom {
+    uint64_t start;      // first point index
+    uint32_t full_rows;  // rows with kWidth points
+    uint32_t rem;        // points in the ragged last row (0 = none)
+};
+
+BQ_HDI TileGeom tile_geom(const Plan& P, uint64_t tile) {
+    TileGeom g;
+    g.start = tile * P.tile_pts;
+    uint64_t left = P.n - g.start;
+    uint64_t npts = left < P.tile_pts ? left : P.tile_pts;
+    g.full_rows = uint32_t(npts / kWidth);
+    g.rem = uint32_t(npts % kWidth);
+    return g;
+}
+
+// First-index-as-double of row r of a tile (exact), including the rule offset.
+BQ_HDI double row_base_index(const Plan& P, const TileGeom& g, uint32_t r) {
+    return double(g.start + uint64_t(r) * kWidth) + P.off;
+}
+
+template <class F>
+struct FunctorOf;
+
+BQ_HDI SinF make_sin(const Plan&) { return SinF{}; }
+BQ_HDI AccF make_acc(const Plan& P) { return AccF{P.p[0], P.p[1]}; }
+BQ_HDI VelF make_vel(const Plan& P) { return VelF{P.p[0], P.p[2]}; }
+BQ_HDI DisF make_dis(const Plan& P) { return DisF{P.p[0], P.p[2]}; }
+BQ_HDI ProfileF make_profile(const Plan& P, const double* table) {
+    return ProfileF{table, int(P.table_len), 1.0 / P.p[0]};
+}
+
+template <class F>
+BQ_HDI F make_functor(const Plan& P, const double* table);
+template <>
+BQ_HDI SinF make_functor<SinF>(const Plan& P, const double*) { return make_sin(P); }
+template <>
+BQ_HDI AccF make_functor<AccF>(const Plan& P, const double*) { return make_acc(P); }
+template <>
+BQ_HDI VelF make_functor<VelF>(const Plan& P, const double*) { return make_vel(P); }
+template <>
+BQ_HDI DisF make_functor<DisF>(const Plan& P, const double*) { return make_dis(P); }
+template <>
+BQ_HDI ProfileF make_functor<ProfileF>(const Plan& P, const double* t) { return make_profile(P, t); }
+
+// Last stage, shared by kernel / CPU / bq_fold_segments: fold the 8 segment
+// pairs in index order, scale by h, add the trapezoid end correction
+// (trap = left + h/2 (f(b) - f(a)); the reference has no trapezoid, only the
+// commented-out include at 4main.c:38).
+template <class F>
+BQ_HDI void finish_result(const Plan& P, const F& f, const double* seg_hi, const double* seg_lo,
+                          bq_result* out) {
+    dd acc{0.0, 0.0};
+    for (int s = 0; s < kSegments; ++s) acc = dd_add(acc, dd{seg_hi[s], seg_lo[s]});
+    dd val = dd_mul_d(acc, P.h);
+    if (P.rule == BQ_RULE_TRAP) {
+        double fb = f.template eval<double>(P.b);
+        double fa = f.template eval<double>(P.a);
+        val = dd_add_d(val, 0.5 * P.h * (fb - fa));
+    }
+    out->raw_sum_hi = acc.hi;
+    out->raw_sum_lo = acc.lo;
+    out->value = val.hi;
+    out->value_lo = val.lo;
+    for (int s = 0; s < kSegments; ++s) {
+        out->seg_hi[s] = seg_hi[s];
+        out->seg_lo[s] = seg_lo[s];
+    }
+    out->n = P.n;
+    out->eval_used = P.eval;
+    out->world = P.world;
+    out->rank = P.rank;
+    out->launches = 1;
+}
+
+}  // namespace bq

@@ -1,0 +1,373 @@
+// The fused definite-integral kernel: ONE launch per GPU per integrate() call.
+//
+//   evaluate f on this rank's share of the n sample points        (hot loop)
+//   -> per-thread dd totals -> warp shuffle -> CTA (smem)
+//   -> thread-block cluster pair through DSMEM                     (chunk sum)
+//   -> ticket; the last cluster folds chunk sums into segment sums
+//   -> publish segment pairs into every peer's comm block over NVLink,
+//      in-kernel epoch barrier, fixed-order fold, *h, rule epilogue -> result
+//
+// Replaces, in the reference: the per-thread loops + host sum of
+// cintegrate.cu:47-98,135-138; riemann_sum + MPI_Send/Recv gather of
+// riemann.cpp:29-44,76,82-85; MPI_Reduce/MPI_Barrier of 4main.c:134,137,200.
+// No tensor-core work exists in this workload (no matrix product), so
+// tcgen05/TMEM are not used; the one bulk transfer (the PROFILE table) goes
+// through a 1-D TMA copy (cp.async.bulk -> UBLKCP).
+#include <cuda_runtime.h>
+#include <stdio.h>
+
+#include <type_traits>
+
+#include "device_state.h"
+#include "ptx.cuh"
+#include "quad_core.cuh"
+#include "quad_launch.h"
+
+namespace bq {
+
+template <class R>
+struct Vec2;
+template <>
+struct __align__(16) Vec2<double> {
+    double x, y;
+};
+template <>
+struct __align__(8) Vec2<float> {
+    float x, y;
+};
+
+__device__ __forceinline__ dd shfl_xor_dd(dd v, int off) {
+    return dd{__shfl_xor_sync(0xffffffffu, v.hi, off), __shfl_xor_sync(0xffffffffu, v.lo, off)};
+}
+
+// Butterfly over the 32 lanes; every lane ends with the same pair.
+__device__ __forceinline__ dd warp_reduce_dd(dd v) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v = dd_add(v, shfl_xor_dd(v, off));
+    return v;
+}
+
+// CTA-wide dd reduction; the result is valid in warp 0 (all lanes).
+__device__ __forceinline__ dd block_reduce_dd(dd v, dd* swarp) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    v = warp_reduce_dd(v);
+    if (lane == 0) swarp[warp] = v;
+    __syncthreads();
+    dd r{0.0, 0.0};
+    if (warp == 0) {
+        r = lane < kThreads / 32 ? swarp[lane] : dd{0.0, 0.0};
+#pragma unroll
+        for (int off = 4; off >= 1; off >>= 1) r = dd_add(r, shfl_xor_dd(r, off));
+    }
+    __syncthreads();
+    return r;
+}
+
+template <class F, class R, int MODE>
+struct PartWorker {
+    static constexpr bool kRotate = (MODE == BQ_EVAL_ROTATE);
+
+    const Plan& P;        // shared-memory copy (per-tile geometry only)
+    const F& f;
+    Vec2<R> (*sSC)[kMaxRows];
+    double (*sX0)[kMaxRows];
+    const double h, a;    // register copies for the hot loops
+    // column constants
+    R cj[kCols], sj[kCols];
+    double dx[kCols];     // ROTATE: x offset of the column; DIRECT: column index as double
+
+    __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R> (*sc)[kMaxRows],
+                                          double (*x0)[kMaxRows])
+        : P(P_), f(f_), sSC(sc), sX0(x0), h(P_.h), a(P_.a) {
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) {
+            const double col = double(threadIdx.x + kThreads * j);
+            if (kRotate) {
+                dx[j] = col * h;
+                double s, c;
+                sincos(f.angle(dx[j]), &s, &c);
+                cj[j] = R(c);
+                sj[j] = R(s);
+            } else {
+                dx[j] = col;
+                cj[j] = R(0);
+                sj[j] = R(0);
+            }
+        }
+    }
+
+    // Row bases of `tile` -> sSC/sX0[buf]; done by two warps that rotate with
+    // the tile index so the fp64 cost is spread over the four SMSPs.
+    __device__ __forceinline__ void bases(uint64_t tile, int buf) const {
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        const int bw = int(tile & 3) * 2;
+        if (warp != bw && warp != bw + 1) return;
+        const TileGeom g = tile_geom(P, tile);
+        const uint32_t rows = g.full_rows + (g.rem ? 1u : 0u);
+        const uint32_t k = uint32_t(warp - bw) * 32u + lane;
+        if (k < rows) {
+            const double x0 = fma(row_base_index(P, g, k), h, a);
+            double s, c;
+            sincos(f.angle(x0), &s, &c);
+            sSC[buf][k] = Vec2<R>{R(s), R(c)};
+            sX0[buf][k] = x0;
+        }
+    }
+
+    __device__ __forceinline__ double tile_sum(uint64_t tile, int buf) const {
+        const TileGeom g = tile_geom(P, tile);
+        TileAcc<R> acc;
+        acc.clear();
+        if (kRotate) {
+#pragma unroll 2
+            for (uint32_t r = 0; r < g.full_rows; ++r) {
+                const Vec2<R> sc = sSC[buf][r];
+                const double x0 = F::kNeedX ? sX0[buf][r] : 0.0;
+                R v[kCols];
+#pragma unroll
+                for (int j = 0; j < kCols; ++j)
+                    v[j] = point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]);
+                acc.add_row(v);
+            }
+            if (g.rem) {
+                const Vec2<R> sc = sSC[buf][g.full_rows];
+                const double x0 = sX0[buf][g.full_rows];
+#pragma unroll
+                for (int j = 0; j < kCols; ++j)
+                    if (threadIdx.x + kThreads * j < g.rem)
+                        acc.add_one(j, point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]));
+            }
+        } else {
+            double rb = row_base_index(P, g, 0);
+#pragma unroll 2
+            for (uint32_t r = 0; r < g.full_rows; ++r) {
+                R v[kCols];
+#pragma unroll
+                for (int j = 0; j < kCols; ++j) v[j] = point_direct<F, R>(f, rb, dx[j], h, a);
+                acc.add_row(v);
+                rb += double(kWidth);
+            }
+            if (g.rem) {
+#pragma unroll
+                for (int j = 0; j < kCols; ++j)
+                    if (threadIdx.x + kThreads * j < g.rem)
+                        acc.add_one(j, point_direct<F, R>(f, rb, dx[j], h, a));
+            }
+        }
+        return acc.flush();
+    }
+
+    // All tiles of one part; returns this thread's dd total.
+    __device__ __forceinline__ dd run(uint32_t part) const {
+        uint64_t lo, hi;
+        part_tiles(P, part, lo, hi);
+        dd total{0.0, 0.0};
+        if (kRotate) {
+            if (lo < hi) bases(lo, 0);
+            __syncthreads();
+            int buf = 0;
+            for (uint64_t t = lo; t < hi; ++t) {
+                if (t + 1 < hi) bases(t + 1, buf ^ 1);   // overlaps this tile's rows
+                total = dd_add_d(total, tile_sum(t, buf));
+                __syncthreads();
+                buf ^= 1;
+            }
+        } else {
+            for (uint64_t t = lo; t < hi; ++t) total = dd_add_d(total, tile_sum(t, 0));
+        }
+        return total;
+    }
+};
+
+template <class F, class R, int MODE>
+__global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
+    __shared__ Plan P;
+    __shared__ Vec2<R> sSC[2][kMaxRows];
+    __shared__ double sX0[2][kMaxRows];
+    __shared__ dd swarp[kThreads / 32];
+    __shared__ __align__(16) dd sPeer[2];          // DSMEM mailbox (leader CTA), by chunk parity
+    __shared__ dd sSeg[kSegments];
+    __shared__ int sIsLast;
+    constexpr bool kIsProfile = std::is_same<F, ProfileF>::value;
+    __shared__ __align__(16) double sTable[kIsProfile ? kMaxTable : 2];
+    __shared__ __align__(8) uint64_t sBar;
+
+    const int tid = threadIdx.x;
+    const uint32_t crank = ptx::cluster_ctarank();
+    const uint32_t csize = ptx::cluster_nctarank();
+
+    if (blockIdx.x == 0 && tid == 0) st.result->t_start_ns = ptx::globaltimer();
+
+    // ---- plan (+ table) into shared memory ---------------------------------
+    {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(st.plan);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&P);
+        for (int i = tid; i < int(sizeof(Plan) / 4); i += kThreads) dst[i] = __ldg(src + i);
+    }
+    if (kIsProfile && tid == 0) ptx::mbar_init(&sBar, 1);
+    __syncthreads();
+    if (kIsProfile) {
+        // One 1-D TMA bulk copy brings the whole table (14.4 KB by default).
+        const uint32_t bytes = ((P.table_len + 1u) & ~1u) * 8u;
+        if (tid == 0) {
+            ptx::mbar_expect_tx(&sBar, bytes);
+            ptx::tma_bulk_g2s(sTable, st.table, bytes, &sBar);
+        }
+        ptx::mbar_wait(&sBar, 0);
+    }
+
+    const F f = make_functor<F>(P, sTable);
+    const PartWorker<F, R, MODE> worker(P, f, sSC, sX0);
+
+    const uint32_t cluster_id = blockIdx.x / csize;
+    const uint32_t n_clusters = gridDim.x / csize;
+
+    // ---- chunks ------------------------------------------------------------
+    uint32_t iter = 0;
+    for (uint32_t chunk = P.chunk_lo + cluster_id; chunk < P.chunk_hi; chunk += n_clusters, ++iter) {
+        dd cv;
+        if (csize == 2) {
+            const dd mine = block_reduce_dd(worker.run(chunk * kPartsPerChunk + crank), swarp);
+            if (crank == 1 && tid == 0)
+                ptx::st_dsmem_f64x2(ptx::mapa(&sPeer[iter & 1], 0), mine.hi, mine.lo);
+            // One cluster barrier per chunk: release of the DSMEM store, and
+            // (two iterations later) licence to overwrite the same mailbox.
+            ptx::cluster_sync_all();
+            cv = mine;
+            if (crank == 0 && tid == 0) cv = dd_add(mine, sPeer[iter & 1]);
+        } else {
+            const dd p0 = block_reduce_dd(worker.run(chunk * kPartsPerChunk + 0), swarp);
+            const dd p1 = block_reduce_dd(worker.run(chunk * kPartsPerChunk + 1), swarp);
+            cv = dd_add(p0, p1);
+        }
+        if (crank == 0 && tid == 0) st.partials[chunk] = cv;
+    }
+    if (crank != 0) return;
+
+    // ---- ticket: who is last? ------------------------------------------------
+    if (tid == 0) {
+        __threadfence();
+        const unsigned int t = atomicAdd(st.ticket, 1u);
+        sIsLast = (t == n_clusters - 1);
+    }
+    __syncthreads();
+    if (!sIsLast) return;
+    __threadfence();
+
+    // ---- segment sums: one warp per owned segment, fixed order ---------------
+    const int warp = tid >> 5, lane = tid & 31;
+    if (tid < kSegments) sSeg[tid] = dd{0.0, 0.0};
+    __syncthreads();
+    {
+        const uint32_t seg = P.seg_lo + warp;
+        if (seg < P.seg_hi) {
+            dd acc{0.0, 0.0};
+            const uint32_t c0 = seg * kChunksPerSegment;
+            for (uint32_t c = c0 + lane; c < c0 + kChunksPerSegment; c += 32) {
+                double hi, lo;
+                ptx::ld_relaxed_sys_f64x2(reinterpret_cast<const double*>(st.partials + c), hi, lo);
+                acc = dd_add(acc, dd{hi, lo});
+            }
+            acc = warp_reduce_dd(acc);
+            if (lane == 0) sSeg[seg] = acc;
+        }
+    }
+    __syncthreads();
+    if (warp != 0) return;
+
+    int status = BQ_OK;
+    const bool exchange = P.world > 1 && !(P.flags & kFlagLocalOnly);
+    if (exchange) {
+        // ---- cross-GPU: publish, barrier, gather -----------------------------
+        const uint64_t epoch = st.comm->epoch;
+        const int par = int(epoch & 1);
+        if (lane < P.world && !(P.flags & kFlagSkipPublish)) {
+            CommBlock* peer = st.peers[lane];
+            for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s)
+                ptx::st_relaxed_sys_f64x2(&peer->slots[par][s][0], sSeg[s].hi, sSeg[s].lo);
+            ptx::red_release_sys_add(&peer->arrived, 1ull);
+        }
+        __syncwarp();
+        const uint64_t target = uint64_t(P.world) * (epoch + 1);
+        const uint64_t t0 = ptx::globaltimer();
+        const uint64_t limit = uint64_t(P.timeout_ms) * 1000000ull;
+        if (lane == 0) {
+            while (ptx::ld_acquire_sys(&st.comm->arrived) < target) {
+                if (ptx::globaltimer() - t0 > limit) {
+                    status = BQ_ERR_TIMEOUT;
+                    break;
+                }
+            }
+        }
+        status = __shfl_sync(0xffffffffu, status, 0);
+        if (lane < kSegments) {
+            double hi, lo;
+            ptx::ld_relaxed_sys_f64x2(&st.comm->slots[par][lane][0], hi, lo);
+            sSeg[lane] = dd{hi, lo};
+        }
+        __syncwarp();
+        if (lane == 0) st.comm->epoch = epoch + 1;
+    }
+
+    if (lane == 0) {
+        double hi[kSegments], lo[kSegments];
+        for (int s = 0; s < kSegments; ++s) hi[s] = sSeg[s].hi, lo[s] = sSeg[s].lo;
+        if (st.seg_out) {
+            for (int s = 0; s < kSegments; ++s) st.seg_out[2 * s] = hi[s], st.seg_out[2 * s + 1] = lo[s];
+        }
+        finish_result<F>(P, f, hi, lo, st.result);
+        if (status != BQ_OK) st.result->value = nan("");
+        st.result->status = status;
+        *st.ticket = 0u;
+        st.result->t_end_ns = ptx::globaltimer();
+    }
+}
+
+// ---- dispatch ----------------------------------------------------------------
+
+template <class F, class R, int MODE>
+static cudaError_t launch_one(const DeviceState& st, const LaunchConfig& cfg, cudaStream_t stream) {
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(cfg.grid, 1, 1);
+    lc.blockDim = dim3(kThreads, 1, 1);
+    lc.dynamicSmemBytes = 0;
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cfg.cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    return cudaLaunchKernelEx(&lc, quad_kernel<F, R, MODE>, st);
+}
+
+template <class F>
+static cudaError_t launch_f(const Plan& P, const DeviceState& st, const LaunchConfig& cfg,
+                            cudaStream_t stream) {
+    const bool rot = P.eval == BQ_EVAL_ROTATE;
+    if constexpr (F::kTrig) {
+        if (P.dtype == BQ_F64)
+            return rot ? launch_one<F, double, BQ_EVAL_ROTATE>(st, cfg, stream)
+                       : launch_one<F, double, BQ_EVAL_DIRECT>(st, cfg, stream);
+        return rot ? launch_one<F, float, BQ_EVAL_ROTATE>(st, cfg, stream)
+                   : launch_one<F, float, BQ_EVAL_DIRECT>(st, cfg, stream);
+    } else {
+        if (P.dtype == BQ_F64) return launch_one<F, double, BQ_EVAL_DIRECT>(st, cfg, stream);
+        return launch_one<F, float, BQ_EVAL_DIRECT>(st, cfg, stream);
+    }
+}
+
+cudaError_t launch_quad(const Plan& P, const DeviceState& st, const LaunchConfig& cfg,
+                        cudaStream_t stream) {
+    switch (P.integrand) {
+        case BQ_F_SIN: return launch_f<SinF>(P, st, cfg, stream);
+        case BQ_F_ACC: return launch_f<AccF>(P, st, cfg, stream);
+        case BQ_F_VEL: return launch_f<VelF>(P, st, cfg, stream);
+        case BQ_F_DIS: return launch_f<DisF>(P, st, cfg, stream);
+        case BQ_F_PROFILE: return launch_f<ProfileF>(P, st, cfg, stream);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace bq

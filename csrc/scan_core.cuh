@@ -1,0 +1,102 @@
+// Arithmetic of the fused scan shared by scan_kernel.cu and cpu_scan.cpp.
+//
+// A run of samples is summarised by (p, q, cnt):
+//   p   = sum of the values v_k             ("default_sum" increment, 4main.c:105)
+//   q   = sum of the local running sums     ("default_sum_of_sums" increment, 4main.c:185)
+//   cnt = number of samples
+// and two adjacent runs A (earlier), B (later) combine as
+//   p = pA + pB,  q = qA + qB + cntB * pA,  cnt = cntA + cntB
+// which is what the reference's root-side carry fix-up (4main.c:147-154,
+// 211-218) computes one slice at a time.
+#pragma once
+#include "bq_dd.cuh"
+#include "integrands.cuh"
+#include "scan_plan.h"
+
+namespace bq {
+
+struct Run {          // dd precision: used across tiles / segments
+    dd p, q;
+    double cnt;       // exact (integers below 2^53)
+};
+
+BQ_HD Run run_identity() { return Run{dd{0.0, 0.0}, dd{0.0, 0.0}, 0.0}; }
+
+BQ_HD Run run_combine(const Run& A, const Run& B) {
+    Run r;
+    r.p = dd_add(A.p, B.p);
+    r.q = dd_add(dd_add(A.q, B.q), dd_mul_d(A.p, B.cnt));
+    r.cnt = A.cnt + B.cnt;
+    return r;
+}
+
+BQ_HD Run run_from_tile(double s, double w, double cnt) {
+    return Run{dd{s, 0.0}, dd{w, 0.0}, cnt};
+}
+
+struct Run2 {         // plain fp64: used inside one tile
+    double p, q;
+};
+
+// A earlier, B later covering cntB samples.
+BQ_HD Run2 run2_combine(const Run2& A, const Run2& B, double cntB) {
+    return Run2{A.p + B.p, fma(cntB, A.p, A.q + B.q)};
+}
+
+BQ_HDI uint32_t scan_tile_count(const ScanPlan& P, uint64_t tile) {
+    const uint64_t start = tile * uint64_t(kScanTile);
+    const uint64_t left = P.n - start;
+    return left < uint64_t(kScanTile) ? uint32_t(left) : uint32_t(kScanTile);
+}
+
+BQ_HDI int scan_segment_of(const ScanPlan& P, uint64_t tile) {
+    int s = 0;
+    for (int k = 1; k < kSegments; ++k) s += (tile >= P.seg_tile[k]) ? 1 : 0;
+    return s;
+}
+
+// Thread-level work on its kScanItems consecutive samples of a tile.
+template <class F>
+BQ_HD void scan_thread_values(const F& f, const ScanPlan& P, uint64_t first_idx, uint32_t k0,
+                              uint32_t m, double (&v)[kScanItems]) {
+#pragma unroll
+    for (int j = 0; j < kScanItems; ++j) {
+        const double x = fma(double(first_idx + uint64_t(j)), P.dx, P.x0);
+        v[j] = (k0 + uint32_t(j) < m) ? f.template eval<double>(x) : 0.0;
+    }
+}
+
+// Phase A: (sum v, sum v*(m-k)) of this thread's samples.
+BQ_HD void scan_thread_aggregate(const double (&v)[kScanItems], uint32_t k0, uint32_t m, double& s,
+                                 double& w) {
+    s = 0.0;
+    w = 0.0;
+#pragma unroll
+    for (int j = 0; j < kScanItems; ++j) {
+        const uint32_t k = k0 + uint32_t(j);
+        const double wt = k < m ? double(m - k) : 0.0;
+        s += v[j];
+        w = fma(v[j], wt, w);
+    }
+}
+
+// Phase B: local inclusive scans lp_j = sum_{i<=j} v_i, lq_j = sum_{i<=j} lp_i.
+BQ_HD void scan_thread_local(const double (&v)[kScanItems], double (&lp)[kScanItems],
+                             double (&lq)[kScanItems]) {
+    double p = 0.0, q = 0.0;
+#pragma unroll
+    for (int j = 0; j < kScanItems; ++j) {
+        p += v[j];
+        q += p;
+        lp[j] = p;
+        lq[j] = q;
+    }
+}
+
+// Tile exclusive prefix from the segment base and the in-segment prefix.
+BQ_HD Run2 scan_tile_exclusive(const Run& base, const Run& pre) {
+    const Run r = run_combine(base, pre);
+    return Run2{dd_to_double(r.p), dd_to_double(r.q)};
+}
+
+}  // namespace bq

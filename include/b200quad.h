@@ -1,0 +1,227 @@
+/* b200quad — Blackwell-native numerical integration: public C ABI.
+ *
+ * Everything the Python layer, the torch ops and the CLIs do goes through the
+ * entry points declared here.  Reference parity notes cite the upstream
+ * Excalibur1224/Cuda-v-MPI sources as file:line.
+ */
+#ifndef B200QUAD_H_
+#define B200QUAD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- enums ------------------------------------------------------------- */
+
+/* Integrand library.  SIN is the hard-coded integrand of riemann.cpp:37 and
+ * cintegrate.cu:68; ACC/VEL/DIS are the analytic train model of
+ * riemann.cpp:103-116; PROFILE is the 1801-entry velocity table of ex4vel.h
+ * lerped as faccel() does (4main.c:262-268, cintegrate.cu:36-44). */
+enum bq_integrand {
+    BQ_F_SIN = 0,
+    BQ_F_ACC = 1,
+    BQ_F_VEL = 2,
+    BQ_F_DIS = 3,
+    BQ_F_PROFILE = 4,
+    BQ_F_COUNT = 5
+};
+
+/* Quadrature rule.  The reference only has LEFT (riemann.cpp:36-39). */
+enum bq_rule { BQ_RULE_LEFT = 0, BQ_RULE_RIGHT = 1, BQ_RULE_MID = 2, BQ_RULE_TRAP = 3 };
+
+/* Arithmetic.  F64: fp64 evaluation, dd-compensated combines.  F32C: fp32
+ * evaluation with pairwise+Kahan per-thread accumulation, promoted to fp64 at
+ * the first cross-thread combine. */
+enum bq_dtype { BQ_F64 = 0, BQ_F32C = 1 };
+
+/* How f is evaluated.  DIRECT: x_i formed and f(x_i) called per point (works
+ * for every integrand).  ROTATE: for trig integrands, sin/cos of each point
+ * are produced by an exact-angle-sum rotation of an accurately computed tile
+ * base (3 fp64 ops per point instead of a full sin()).  AUTO picks ROTATE
+ * when the integrand supports it and n is large enough to amortise set-up. */
+enum bq_eval { BQ_EVAL_AUTO = 0, BQ_EVAL_DIRECT = 1, BQ_EVAL_ROTATE = 2 };
+
+enum bq_status {
+    BQ_OK = 0,
+    BQ_ERR_INVALID = 1,      /* bad argument */
+    BQ_ERR_CUDA = 2,         /* a CUDA runtime call failed; see bq_last_error() */
+    BQ_ERR_TIMEOUT = 3,      /* a peer never arrived at the in-kernel barrier */
+    BQ_ERR_UNSUPPORTED = 4,
+    BQ_ERR_RANGE = 5         /* integrand evaluated outside its table */
+};
+
+/* ---- job / result ------------------------------------------------------ */
+
+#define BQ_SEGMENTS 8          /* fixed top-level split of the index space     */
+#define BQ_MAX_WORLD 8
+
+typedef struct bq_job {
+    int32_t integrand;         /* enum bq_integrand */
+    int32_t rule;              /* enum bq_rule */
+    int32_t dtype;             /* enum bq_dtype */
+    int32_t eval;              /* enum bq_eval */
+    double a, b;               /* interval */
+    uint64_t n;                /* number of sub-intervals, 1 .. 2^40 */
+    /* integrand parameters; 0 means "reference default":
+     *  ACC/VEL/DIS: p[0]=tscale p[1]=ascale p[2]=vscale (riemann.cpp:7-9)
+     *  PROFILE    : p[0]=table spacing in x units (1.0 s, ex4vel.h:1-5) */
+    double p[4];
+} bq_job;
+
+typedef struct bq_result {
+    double value;              /* the integral */
+    double value_lo;           /* low word of the dd result (value+value_lo) */
+    double raw_sum_hi;         /* sum of f(x_i) before multiplying by h */
+    double raw_sum_lo;
+    double seg_hi[BQ_SEGMENTS];/* the 8 fixed segment sums (debug / parity) */
+    double seg_lo[BQ_SEGMENTS];
+    uint64_t t_start_ns;       /* %globaltimer at kernel entry (first CTA)    */
+    uint64_t t_end_ns;         /* %globaltimer when the result was written    */
+    uint64_t n;                /* echo */
+    int32_t status;            /* enum bq_status, written by the kernel       */
+    int32_t eval_used;         /* enum bq_eval actually used                  */
+    int32_t world;             /* ranks that contributed                      */
+    int32_t rank;
+    float device_ms;           /* cudaEvent time of the launch (sync calls)   */
+    int32_t launches;          /* kernels launched for this call (always 1)   */
+    uint64_t reserved[2];
+} bq_result;
+
+/* ---- cumulative integration (scan) -------------------------------------
+ * Capability of 4main.c:76-225: sample f on a uniform grid, running sum
+ * P[i] = sum_{k<=i} f(x_k) ("default_sum"), and running sum of that,
+ * Q[i] = sum_{k<=i} P[k] ("default_sum_of_sums"), both over the whole grid
+ * even when the grid is split over several GPUs. */
+typedef struct bq_scan_job {
+    int32_t integrand;
+    int32_t replicate;         /* 1: every rank ends with the whole table (MPI_Bcast, 4main.c:157,221) */
+    int32_t want_samples;      /* 1: also store f(x_i) ("InterpProfile", 4main.c:82-86) */
+    int32_t reserved;
+    double x0, dx;             /* x_i = x0 + i*dx */
+    uint64_t n;                /* samples */
+    double p[4];
+} bq_scan_job;
+
+typedef struct bq_scan_result {
+    double p_last;             /* P[n-1] */
+    double q_last;             /* Q[n-1] */
+    double p_second_last;      /* P[n-2] — the element 4main.c:241 prints */
+    uint64_t slice_begin;      /* this rank's slice of the tables */
+    uint64_t slice_end;
+    uint64_t t_start_ns, t_end_ns;
+    int32_t status;
+    int32_t world;
+    int32_t rank;
+    float device_ms;
+    uint64_t reserved[2];
+} bq_scan_result;
+
+/* ---- library-level ----------------------------------------------------- */
+
+const char* bq_version(void);
+const char* bq_last_error(void);               /* thread-local message */
+int bq_cuda_device_count(void);                /* 0 when no driver / no GPU */
+const double* bq_default_profile(int* len);    /* the 1801-entry table */
+/* Bytes moved host->device per call (the parameter block). */
+size_t bq_sizeof_params(void);
+
+/* Closed-form / exactly-rounded oracles used by the tests and the CLIs. */
+double bq_oracle_sin_sum(double a, double b, uint64_t n, int rule);
+
+/* ---- CPU backend (same summation tree as the kernels) ------------------ */
+
+/* Whole job on the host with `threads` worker threads. */
+int bq_cpu_integrate(const bq_job* job, int threads, bq_result* out);
+/* Only the segments owned by `rank` of `world`; seg_hi/seg_lo of the others
+ * are left 0.  Used by the gloo / multi-process CPU path. */
+int bq_cpu_integrate_segments(const bq_job* job, int rank, int world, int threads, bq_result* out);
+/* Fold 8 segment pairs (in order) + rule epilogue -> value.  The same code the
+ * kernel's last stage runs. */
+int bq_fold_segments(const bq_job* job, const double* seg_hi, const double* seg_lo, bq_result* out);
+int bq_cpu_cumulative(const bq_scan_job* job, int threads, double* P, double* Q, double* samples,
+                      bq_scan_result* out);
+
+/* ---- CUDA contexts ----------------------------------------------------- */
+
+typedef struct bq_ctx bq_ctx;
+
+/* One context per (process, device).  Allocates: param block, partials,
+ * ticket, result block, comm block (peer-visible), pinned staging ring. */
+int bq_ctx_create(int device, bq_ctx** out);
+void bq_ctx_destroy(bq_ctx* ctx);
+int bq_ctx_device(const bq_ctx* ctx);
+/* Stream used by the synchronous calls (a cudaStream_t). */
+void* bq_ctx_stream(const bq_ctx* ctx);
+/* Replace the PROFILE table (len <= 4096 entries). */
+int bq_ctx_set_profile(bq_ctx* ctx, const double* table, int len);
+/* Launch configuration knobs (0 = default): CTAs per SM, cluster size (1|2),
+ * rows per tile.  For tuning / tests; results do not depend on the first two. */
+int bq_ctx_configure(bq_ctx* ctx, int ctas_per_sm, int cluster, int rows_per_tile);
+/* In-kernel barrier time-out in milliseconds (default 2000). */
+int bq_ctx_set_timeout_ms(bq_ctx* ctx, int ms);
+
+/* Synchronous: pinned params -> H2D -> one fused kernel -> D2H result. */
+int bq_integrate(bq_ctx* ctx, const bq_job* job, bq_result* out);
+/* Asynchronous on `stream` (cudaStream_t; NULL = ctx stream): enqueues the
+ * H2D of the params, the kernel and the D2H of the result into pinned memory.
+ * bq_result_fetch() synchronises and copies the result out. */
+int bq_integrate_async(bq_ctx* ctx, const bq_job* job, void* stream);
+int bq_result_fetch(bq_ctx* ctx, bq_result* out);
+/* Device pointer of the result block of the most recent launch. */
+const bq_result* bq_ctx_device_result(const bq_ctx* ctx);
+
+int bq_cumulative(bq_ctx* ctx, const bq_scan_job* job, double* dP, double* dQ, double* dSamples,
+                  bq_scan_result* out);
+int bq_cumulative_async(bq_ctx* ctx, const bq_scan_job* job, double* dP, double* dQ,
+                        double* dSamples, void* stream);
+int bq_scan_result_fetch(bq_ctx* ctx, bq_scan_result* out);
+
+/* ---- multi-GPU: peer wiring --------------------------------------------
+ * Replaces MPI_Send/Recv (riemann.cpp:76,83), MPI_Reduce, MPI_Barrier and
+ * MPI_Bcast (4main.c:134,137,157,200,221): the fused kernels publish their
+ * partials into every peer's comm block with NVLink stores and meet at an
+ * in-kernel epoch barrier. */
+#define BQ_IPC_HANDLE_BYTES 64
+/* Multi-process: export this context's comm block ... */
+int bq_ctx_export_comm(bq_ctx* ctx, unsigned char handle[BQ_IPC_HANDLE_BYTES]);
+/* ... and attach the other ranks' (handles[r] for r != rank; own slot ignored). */
+int bq_ctx_attach_peers(bq_ctx* ctx, int rank, int world,
+                        const unsigned char* handles /* world * 64 bytes */);
+/* Zero this context's barrier state.  Every rank of a world must call it, and
+ * the caller must make sure all have done so (host barrier) before the next
+ * collective call; needed after a BQ_ERR_TIMEOUT. */
+int bq_ctx_reset_comm(bq_ctx* ctx);
+/* Same for an output table the scan replicates into (per call buffer). */
+int bq_ipc_export(void* dptr, unsigned char handle[BQ_IPC_HANDLE_BYTES]);
+int bq_ipc_open(const unsigned char handle[BQ_IPC_HANDLE_BYTES], void** dptr);
+int bq_ipc_close(void* dptr);
+int bq_ctx_set_scan_peers(bq_ctx* ctx, double* const* peerP, double* const* peerQ);
+
+/* Single-process world: one context per listed device, peer access enabled. */
+typedef struct bq_world bq_world;
+int bq_world_create(int ndev, const int* devices, bq_world** out);
+void bq_world_destroy(bq_world* w);
+int bq_world_size(const bq_world* w);
+bq_ctx* bq_world_ctx(bq_world* w, int rank);
+/* Launch on every device, wait for all; out[r] for each rank (may be NULL). */
+int bq_world_integrate(bq_world* w, const bq_job* job, bq_result* out);
+int bq_world_cumulative(bq_world* w, const bq_scan_job* job, double* const* dP, double* const* dQ,
+                        bq_scan_result* out);
+
+/* Baseline comparator pieces (NOT the product path): the same kernel with the
+ * cross-GPU stage disabled leaves its 8/world segment pairs in a device
+ * buffer so an external all-reduce (NCCL) can finish the job. */
+int bq_integrate_local_async(bq_ctx* ctx, const bq_job* job, int rank, int world,
+                             double* dSegPairs /* 2*BQ_SEGMENTS doubles */, void* stream);
+
+/* Fault injection for the time-out path: the next launch on this context
+ * skips its publish step (its peers must report BQ_ERR_TIMEOUT). */
+int bq_ctx_inject_fault(bq_ctx* ctx, int kind);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200QUAD_H_ */

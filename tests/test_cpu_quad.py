@@ -1,0 +1,137 @@
+"""CPU backend of integrate(): same summation tree as the kernel, checked against
+closed forms and math.fsum (oracles 1-2, reference-behaviour 3)."""
+import ctypes as C
+import math
+
+import pytest
+
+import b200quad as bq
+from b200quad import _native
+from b200quad.utils import oracle_sin, oracle_profile, oracle_fsum
+
+RULES = ["left", "right", "mid", "trap"]
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-300)
+
+
+@pytest.mark.parametrize("rule", RULES)
+@pytest.mark.parametrize("ev", ["direct", "rotate"])
+@pytest.mark.parametrize("n", [1, 2, 7, 1000, 1023, 1024, 1025, 65536 + 3, 10**6, (1 << 23) + 11])
+def test_sin_closed_form(rule, ev, n):
+    v = bq.integrate("sin", 0.0, math.pi, n, rule, eval=ev, backend="cpu")
+    ref = oracle_sin(0.0, math.pi, n, rule)
+    assert abs(v - ref) <= 4e-16 * max(abs(ref), 1.0), (v, ref)
+
+
+def test_reference_riemann_value():
+    # riemann.cpp prints 2.00000000000222 at n=1e9 with one worker (rel. err 1.1e-12);
+    # the true left sum is 2 - 1.6e-18.  We must be far closer than the reference.
+    v = bq.integrate("sin", 0.0, math.pi, 10**9, "left", backend="cpu")
+    assert abs(v - 2.0) < 1e-15
+
+
+def test_other_interval_and_sign():
+    v = bq.integrate("sin", 1.0, 2.5, 12345, "mid", backend="cpu")
+    assert rel(v, oracle_sin(1.0, 2.5, 12345, "mid")) < 1e-15
+    v = bq.integrate("sin", 2.5, 1.0, 12345, "mid", backend="cpu")      # reversed: negative h
+    assert rel(v, oracle_sin(2.5, 1.0, 12345, "mid")) < 1e-15
+
+
+@pytest.mark.parametrize("rule", RULES)
+def test_profile_matches_fsum(rule):
+    n = 180_000
+    v = bq.integrate("profile", 0.0, 1800.0, n, rule, backend="cpu")
+    assert rel(v, oracle_profile(n, rule=rule)) < 1e-15
+
+
+def test_profile_reference_numbers():
+    # 4main.c prints 122000.004030 (P=1) .. 122000.003997 (P=8); exactly rounded: 122000.00400000015
+    left = bq.integrate("profile", 0.0, 1800.0, 18_000_000, "left", backend="cpu")
+    trap = bq.integrate("profile", 0.0, 1800.0, 18_000_000, "trap", backend="cpu")
+    assert abs(trap - 122000.00400000015) < 1e-9      # piecewise linear: trapezoid is exact
+    assert abs(left - 122000.004) < 1e-6
+
+
+@pytest.mark.parametrize("name", ["acc", "vel", "dis"])
+@pytest.mark.parametrize("ev", ["direct", "rotate"])
+def test_train_model_against_antiderivative(name, ev):
+    f = bq.models.REGISTRY[name]
+    n = 2_000_000
+    v = bq.integrate(name, 0.0, 900.0, n, "mid", eval=ev, backend="cpu")
+    assert rel(v, f.exact(0.0, 900.0)) < 1e-9         # midpoint rule truncation error ~ h^2
+    d = bq.integrate(name, 0.0, 900.0, n, "mid", eval="direct", backend="cpu")
+    assert rel(v, d) < 1e-14                          # rotate == direct to rounding
+
+
+def test_vel_integral_is_distance():
+    # dis(1800) ~ 122000: the analytic twin of the ex4vel.h table (riemann.cpp:113-116)
+    v = bq.integrate("vel", 0.0, 1800.0, 1_000_000, "trap", backend="cpu")
+    assert abs(v - 122000.0) < 1.0
+
+
+@pytest.mark.parametrize("ev", ["direct", "rotate"])
+def test_fp32_compensated(ev):
+    n = 1 << 22
+    v = bq.integrate("sin", 0.0, math.pi, n, "mid", dtype="fp32", eval=ev, backend="cpu")
+    assert abs(v - 2.0) < 5e-8 * 2.0          # fp32 evaluation, compensated accumulation
+
+
+def _segments(job, rank, world):
+    lib, _ = _native.load()
+    res = _native.Result()
+    assert lib.bq_cpu_integrate_segments(C.byref(job), rank, world, 2, C.byref(res)) == 0
+    return list(res.seg_hi), list(res.seg_lo)
+
+
+@pytest.mark.parametrize("n", [1000, 10**6 + 7])
+def test_world_size_does_not_change_bits(n):
+    job = bq.make_job("sin", 0.0, math.pi, n, "left")
+    whole = bq.integrate_result("sin", 0.0, math.pi, n, "left", backend="cpu")
+    lib, _ = _native.load()
+    for world in (1, 2, 4, 8):
+        hi = [0.0] * 8
+        lo = [0.0] * 8
+        for r in range(world):
+            h, l = _segments(job, r, world)
+            per = 8 // world
+            for s in range(r * per, (r + 1) * per):
+                hi[s], lo[s] = h[s], l[s]
+        out = _native.Result()
+        assert lib.bq_fold_segments(C.byref(job), (C.c_double * 8)(*hi), (C.c_double * 8)(*lo),
+                                    C.byref(out)) == 0
+        assert out.value == whole.value and out.value_lo == whole.value_lo
+
+
+def test_threads_do_not_change_bits():
+    a = bq.integrate("sin", 0.0, math.pi, 3_000_001, backend="cpu", threads=1)
+    b = bq.integrate("sin", 0.0, math.pi, 3_000_001, backend="cpu", threads=7)
+    assert a == b
+
+
+def test_bad_arguments():
+    with pytest.raises(_native.NativeError):
+        bq.integrate("sin", 0.0, 1.0, 0, backend="cpu")
+    with pytest.raises(_native.NativeError):
+        bq.integrate("profile", 0.0, 2000.0, 100, backend="cpu")      # outside the table
+    with pytest.raises(ValueError):
+        bq.integrate("nope", 0.0, 1.0, 10, backend="cpu")
+    with pytest.raises(ValueError):
+        bq.integrate("sin", 0.0, 1.0, 10, "simpson", backend="cpu")
+
+
+def test_python_callable_slow_path():
+    v = bq.integrate(lambda x: x.sin(), 0.0, math.pi, 100_000, "trap")
+    assert rel(v, oracle_sin(0.0, math.pi, 100_000, "trap")) < 1e-13
+
+
+def test_fsum_oracle_agrees_with_closed_form():
+    assert rel(oracle_fsum(math.sin, 0.0, math.pi, 5000, "mid"), oracle_sin(0.0, math.pi, 5000, "mid")) < 1e-15
+
+
+def test_default_profile_table():
+    t = bq.models.default_profile()
+    assert len(t) == 1801 and t[0] == 0.0 and t[1] == 0.002904762
+    assert abs(math.fsum(t) - 122000.004) < 1e-9
+    assert abs(max(t) - 87.14286) < 1e-4
