@@ -452,3 +452,27 @@ int bq_world_integrate(bq_world* w, const bq_job* job, bq_result* out) {
 }
 
 }  // extern "C"
+
+// ---- small device-memory helpers for C callers (the CLIs) -------------------
+extern "C" {
+
+int bq_device_alloc(int device, size_t bytes, void** out) {
+    if (!out) return BQ_ERR_INVALID;
+    DeviceGuard guard(device);
+    BQ_CUDA(cudaMalloc(out, bytes));
+    return BQ_OK;
+}
+
+int bq_device_free(int device, void* p) {
+    DeviceGuard guard(device);
+    BQ_CUDA(cudaFree(p));
+    return BQ_OK;
+}
+
+int bq_device_read(int device, void* host_dst, const void* dev_src, size_t bytes) {
+    DeviceGuard guard(device);
+    BQ_CUDA(cudaMemcpy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost));
+    return BQ_OK;
+}
+
+}  // extern "C"

@@ -20,6 +20,8 @@
 
 namespace bq {
 
+BQ_HD double bq_fma(double a, double b, double c) { return fma(a, b, c); }
+BQ_HD float bq_fma(float a, float b, float c) { return fmaf(a, b, c); }
 BQ_HD double bq_sin(double x) { return sin(x); }
 BQ_HD double bq_cos(double x) { return cos(x); }
 BQ_HD float bq_sin(float x) { return sinf(x); }
@@ -58,10 +60,10 @@ struct DisF {
     static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = true;
     double tscale, vscale;
     template <class R>
-    BQ_HD R eval(R x) const { return R(vscale) * (x - (R(tscale) * bq_sin(x / R(tscale)))); }
+    BQ_HD R eval(R x) const { return R(vscale) * bq_fma(-R(tscale), bq_sin(x / R(tscale)), x); }
     BQ_HD double angle(double x) const { return x / tscale; }
     template <class R>
-    BQ_HD R eval_sc(R x, R s, R) const { return R(vscale) * (x - (R(tscale) * s)); }
+    BQ_HD R eval_sc(R x, R s, R) const { return R(vscale) * bq_fma(-R(tscale), s, x); }
 };
 
 // Uniform-grid table, linear interpolation.  The reference reads
@@ -82,7 +84,7 @@ struct ProfileF {
         R frac = u - R(i);
         R t0 = R(table[i]);
         R t1 = R(table[i + 1]);
-        return t0 + (t1 - t0) * frac;
+        return bq_fma(t1 - t0, frac, t0);
     }
     BQ_HD double angle(double) const { return 0.0; }
     template <class R>

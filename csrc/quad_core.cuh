@@ -8,9 +8,6 @@
 
 namespace bq {
 
-BQ_HD double bq_fma(double a, double b, double c) { return fma(a, b, c); }
-BQ_HD float bq_fma(float a, float b, float c) { return fmaf(a, b, c); }
-
 // ROTATE: f at angle(x0) + angle(dx) from the row base (S, C) = sincos(angle(x0))
 // and the column constants (cj, sj) = cos/sin(angle(dx)).  DMUL + DFMA per
 // needed component; for SinF that is the whole evaluation.

@@ -217,6 +217,11 @@ int bq_world_cumulative(bq_world* w, const bq_scan_job* job, double* const* dP, 
 int bq_integrate_local_async(bq_ctx* ctx, const bq_job* job, int rank, int world,
                              double* dSegPairs /* 2*BQ_SEGMENTS doubles */, void* stream);
 
+/* Device memory for C callers that do not link the CUDA runtime themselves. */
+int bq_device_alloc(int device, size_t bytes, void** out);
+int bq_device_free(int device, void* p);
+int bq_device_read(int device, void* host_dst, const void* dev_src, size_t bytes);
+
 /* Fault injection for the time-out path: the next launch on this context
  * skips its publish step (its peers must report BQ_ERR_TIMEOUT). */
 int bq_ctx_inject_fault(bq_ctx* ctx, int kind);
