@@ -32,31 +32,41 @@ struct CpuWorker {
     const Plan& P;
     F f;
     bool rotate;
-    // column constants per virtual thread
+    // column constants per virtual thread, row rotations per virtual lane
     std::vector<R> cj, sj;
     std::vector<double> dx;
+    SinCos rowrot[32];
+
+    static SinCos host_sc(double ang) {
+        SinCos r;
+        host_sincos(ang, &r.s, &r.c);
+        return r;
+    }
 
     CpuWorker(const Plan& P_, const double* table)
         : P(P_), f(make_functor<F>(P_, table)), rotate(P_.eval == BQ_EVAL_ROTATE) {
         cj.resize(kThreads * kCols);
         sj.resize(kThreads * kCols);
         dx.resize(kThreads * kCols);
-        for (int t = 0; t < kThreads; ++t)
+        SinCos blk[kCols];
+        for (int j = 0; j < kCols; ++j) blk[j] = host_sc(f.angle(double(j * kThreads) * P.h));
+        for (int t = 0; t < kThreads; ++t) {
+            const SinCos mine = host_sc(f.angle(double(t) * P.h));
             for (int j = 0; j < kCols; ++j) {
-                const double col = double(t + kThreads * j);
                 const int idx = t * kCols + j;
                 if (rotate) {
-                    dx[idx] = col * P.h;
-                    double s, c;
-                    host_sincos(f.angle(dx[idx]), &s, &c);
-                    cj[idx] = R(c);
-                    sj[idx] = R(s);
+                    const SinCos cs = rotate_sc(mine, blk[j]);
+                    cj[idx] = R(cs.c);
+                    sj[idx] = R(cs.s);
+                    dx[idx] = double(t + kThreads * j) * P.h;
                 } else {
-                    dx[idx] = col;
                     cj[idx] = R(0);
                     sj[idx] = R(0);
+                    dx[idx] = double(t + kThreads * j);
                 }
             }
+        }
+        for (int l = 0; l < 32; ++l) rowrot[l] = host_sc(f.angle(double(l) * double(kWidth) * P.h));
     }
 
     dd part(uint32_t part_idx) const {
@@ -64,19 +74,18 @@ struct CpuWorker {
         part_tiles(P, part_idx, lo, hi);
         dd total[kThreads];
         for (int t = 0; t < kThreads; ++t) total[t] = dd{0.0, 0.0};
-        R S[kMaxRows + 1], C[kMaxRows + 1];
-        double X0[kMaxRows + 1];
+        R S[kMaxRows], C[kMaxRows];
+        double X0[kMaxRows];
         for (uint64_t tile = lo; tile < hi; ++tile) {
             const TileGeom g = tile_geom(P, tile);
-            const uint32_t rows = g.full_rows + (g.rem ? 1u : 0u);
             if (rotate) {
-                for (uint32_t k = 0; k < rows; ++k) {
-                    const double x0 = fma(row_base_index(P, g, k), P.h, P.a);
-                    double s, c;
-                    host_sincos(f.angle(x0), &s, &c);
-                    S[k] = R(s);
-                    C[k] = R(c);
-                    X0[k] = x0;
+                // every warp of the kernel derives the same row bases for itself
+                const SinCos tb = host_sc(f.angle(fma(double(tile * P.tile_pts) + P.off, P.h, P.a)));
+                for (uint32_t k = 0; k < kMaxRows; ++k) {
+                    const SinCos rb = rotate_sc(tb, rowrot[k]);
+                    S[k] = R(rb.s);
+                    C[k] = R(rb.c);
+                    X0[k] = fma(row_base_index(P, g, k), P.h, P.a);
                 }
             }
             for (int t = 0; t < kThreads; ++t) {

@@ -27,9 +27,9 @@
 namespace bq {
 
 constexpr int kThreads = 256;                 // threads per CTA (fixed: part of the tree)
-constexpr int kCols = 4;                      // columns per thread
+constexpr int kCols = 8;                      // columns per thread
 constexpr int kWidth = kThreads * kCols;      // points per row
-constexpr int kMaxRows = 64;                  // rows per tile upper bound
+constexpr int kMaxRows = 32;                  // rows per tile upper bound (one per lane)
 constexpr int kPartsPerChunk = 2;             // == cluster size when clusters are on
 constexpr int kChunks = 2368;                 // 8 segments x 296 chunks (= 16 x 148 SMs)
 constexpr int kParts = kChunks * kPartsPerChunk;

@@ -8,6 +8,22 @@
 
 namespace bq {
 
+// sin and cos of one angle.
+struct SinCos {
+    double s, c;
+};
+
+// sin/cos of (angle of `base` + angle of `rot`): 2 DMUL + 2 DFMA.
+BQ_HD SinCos rotate_sc(SinCos base, SinCos rot) {
+    return SinCos{fma(base.c, rot.s, base.s * rot.c), fma(-base.s, rot.s, base.c * rot.c)};
+}
+
+// ROTATE mode builds every sample's sin/cos from accurately computed anchors by
+// exact angle sums, never by a recurrence longer than two rotations:
+//   tile base      sincos(angle(x_tile))                 libm/libdevice, once per tile
+//   row base       rotate(tile base, sincos(angle(r * kWidth * h)))
+//   column const   rotate(sincos(angle(t * h)), sincos(angle(j * kThreads * h)))
+//   sample         rotate(row base, column const)        (point_rotate below)
 // ROTATE: f at angle(x0) + angle(dx) from the row base (S, C) = sincos(angle(x0))
 // and the column constants (cj, sj) = cos/sin(angle(dx)).  DMUL + DFMA per
 // needed component; for SinF that is the whole evaluation.
@@ -34,6 +50,13 @@ BQ_HD R point_direct(const F& f, double rowbase, double col, double h, double a)
 //   fp32: the kCols values of a row are summed pairwise, the row sums are
 //         Kahan-accumulated in fp32, and the compensated value is promoted to
 //         fp64 at the end of a tile.
+// Fixed pairwise (balanced-tree) sum of the kCols values of one row.
+template <class R>
+BQ_HD R pairwise_cols(const R (&v)[kCols]) {
+    static_assert(kCols == 8, "pairwise_cols is written for 8 columns");
+    return ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+}
+
 template <class R>
 struct TileAcc;
 
@@ -49,15 +72,7 @@ struct TileAcc<double> {
         for (int j = 0; j < kCols; ++j) a[j] += v[j];
     }
     BQ_HD void add_one(int j, double v) { a[j] += v; }
-    BQ_HD double flush() const {
-        double s = 0.0;
-        if (kCols == 4) {
-            s = (a[0] + a[1]) + (a[2] + a[3]);
-        } else {
-            for (int j = 0; j < kCols; ++j) s += a[j];
-        }
-        return s;
-    }
+    BQ_HD double flush() const { return pairwise_cols<double>(a); }
 };
 
 template <>
@@ -65,14 +80,7 @@ struct TileAcc<float> {
     float sum, comp;
     BQ_HD void clear() { sum = 0.f, comp = 0.f; }
     BQ_HD void add_row(const float (&v)[kCols]) {
-        float r;
-        if (kCols == 4) {
-            r = (v[0] + v[1]) + (v[2] + v[3]);
-        } else {
-            r = 0.f;
-            for (int j = 0; j < kCols; ++j) r += v[j];
-        }
-        kahan_add(sum, comp, r);
+        kahan_add(sum, comp, pairwise_cols<float>(v));
     }
     BQ_HD void add_one(int, float v) { kahan_add(sum, comp, v); }
     BQ_HD double flush() const { return double(sum) - double(comp); }

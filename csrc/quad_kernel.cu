@@ -69,48 +69,65 @@ struct PartWorker {
 
     const Plan& P;        // shared-memory copy (per-tile geometry only)
     const F& f;
-    Vec2<R> (*sSC)[kMaxRows];
-    double (*sX0)[kMaxRows];
+    Vec2<R>* wSC;         // this warp's private row bases: [2][kMaxRows]
+    double* wX0;          // this warp's private row x0:    [2][kMaxRows]
     const double h, a;    // register copies for the hot loops
     // column constants
     R cj[kCols], sj[kCols];
     double dx[kCols];     // ROTATE: x offset of the column; DIRECT: column index as double
+    SinCos rowrot;        // ROTATE: rotation of row `lane` relative to the tile base
 
-    __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R> (*sc)[kMaxRows],
-                                          double (*x0)[kMaxRows])
-        : P(P_), f(f_), sSC(sc), sX0(x0), h(P_.h), a(P_.a) {
+    __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R>* sc, double* x0)
+        : P(P_), f(f_), wSC(sc), wX0(x0), h(P_.h), a(P_.a) {
+        const int lane = threadIdx.x & 31;
+        if (kRotate) {
+            // Two sincos per thread for all kCols columns: the thread's own
+            // offset, and (lane & 7)'s block offset shared through shuffles.
+            SinCos mine, blk;
+            sincos(f.angle(double(threadIdx.x) * h), &mine.s, &mine.c);
+            sincos(f.angle(double((lane & (kCols - 1)) * kThreads) * h), &blk.s, &blk.c);
 #pragma unroll
-        for (int j = 0; j < kCols; ++j) {
-            const double col = double(threadIdx.x + kThreads * j);
-            if (kRotate) {
-                dx[j] = col * h;
-                double s, c;
-                sincos(f.angle(dx[j]), &s, &c);
-                cj[j] = R(c);
-                sj[j] = R(s);
-            } else {
-                dx[j] = col;
+            for (int j = 0; j < kCols; ++j) {
+                SinCos bj;
+                bj.s = __shfl_sync(0xffffffffu, blk.s, j);
+                bj.c = __shfl_sync(0xffffffffu, blk.c, j);
+                const SinCos cs = rotate_sc(mine, bj);
+                cj[j] = R(cs.c);
+                sj[j] = R(cs.s);
+                dx[j] = double(threadIdx.x + kThreads * j) * h;
+            }
+            sincos(f.angle(double(lane) * double(kWidth) * h), &rowrot.s, &rowrot.c);
+        } else {
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) {
+                dx[j] = double(threadIdx.x + kThreads * j);
                 cj[j] = R(0);
                 sj[j] = R(0);
             }
+            rowrot = SinCos{0.0, 1.0};
         }
     }
 
-    // Row bases of `tile` -> sSC/sX0[buf]; done by two warps that rotate with
-    // the tile index so the fp64 cost is spread over the four SMSPs.
-    __device__ __forceinline__ void bases(uint64_t tile, int buf) const {
-        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-        const int bw = int(tile & 3) * 2;
-        if (warp != bw && warp != bw + 1) return;
-        const TileGeom g = tile_geom(P, tile);
-        const uint32_t rows = g.full_rows + (g.rem ? 1u : 0u);
-        const uint32_t k = uint32_t(warp - bw) * 32u + lane;
-        if (k < rows) {
-            const double x0 = fma(row_base_index(P, g, k), h, a);
-            double s, c;
-            sincos(f.angle(x0), &s, &c);
-            sSC[buf][k] = Vec2<R>{R(s), R(c)};
-            sX0[buf][k] = x0;
+    // Accurate sincos of the base angle of tile `first + lane` (one pass serves 32 tiles).
+    __device__ __forceinline__ SinCos group_bases(uint64_t first, uint64_t hi) const {
+        const uint64_t tile = first + (threadIdx.x & 31);
+        SinCos g{0.0, 1.0};
+        if (tile < hi) {
+            const double xt = fma(double(tile * P.tile_pts) + P.off, h, a);
+            sincos(f.angle(xt), &g.s, &g.c);
+        }
+        return g;
+    }
+
+    // Row bases of one tile: lane r rotates the tile base by r rows (4 fp64 ops)
+    // and parks the pair in this warp's private shared-memory slot.
+    __device__ __forceinline__ void row_bases(uint64_t tile, SinCos tb, int buf) const {
+        const int lane = threadIdx.x & 31;
+        const SinCos rb = rotate_sc(tb, rowrot);
+        wSC[buf * kMaxRows + lane] = Vec2<R>{R(rb.s), R(rb.c)};
+        if (F::kNeedX) {
+            const TileGeom g = tile_geom(P, tile);
+            wX0[buf * kMaxRows + lane] = fma(row_base_index(P, g, lane), h, a);
         }
     }
 
@@ -119,10 +136,12 @@ struct PartWorker {
         TileAcc<R> acc;
         acc.clear();
         if (kRotate) {
-#pragma unroll 2
+            const Vec2<R>* sc_row = wSC + buf * kMaxRows;
+            const double* x0_row = wX0 + buf * kMaxRows;
+#pragma unroll 4
             for (uint32_t r = 0; r < g.full_rows; ++r) {
-                const Vec2<R> sc = sSC[buf][r];
-                const double x0 = F::kNeedX ? sX0[buf][r] : 0.0;
+                const Vec2<R> sc = sc_row[r];
+                const double x0 = F::kNeedX ? x0_row[r] : 0.0;
                 R v[kCols];
 #pragma unroll
                 for (int j = 0; j < kCols; ++j)
@@ -130,8 +149,8 @@ struct PartWorker {
                 acc.add_row(v);
             }
             if (g.rem) {
-                const Vec2<R> sc = sSC[buf][g.full_rows];
-                const double x0 = sX0[buf][g.full_rows];
+                const Vec2<R> sc = sc_row[g.full_rows];
+                const double x0 = F::kNeedX ? x0_row[g.full_rows] : 0.0;
 #pragma unroll
                 for (int j = 0; j < kCols; ++j)
                     if (threadIdx.x + kThreads * j < g.rem)
@@ -157,19 +176,32 @@ struct PartWorker {
         return acc.flush();
     }
 
-    // All tiles of one part; returns this thread's dd total.
+    // All tiles of one part; returns this thread's dd total.  In ROTATE mode a
+    // warp is self-sufficient (its own bases, its own shared-memory slot), so
+    // the tile loop has no CTA-wide barrier.
     __device__ __forceinline__ dd run(uint32_t part) const {
         uint64_t lo, hi;
         part_tiles(P, part, lo, hi);
         dd total{0.0, 0.0};
         if (kRotate) {
-            if (lo < hi) bases(lo, 0);
-            __syncthreads();
+            if (lo >= hi) return total;
+            uint64_t gfirst = lo;
+            SinCos grp = group_bases(gfirst, hi);
+            row_bases(lo, SinCos{__shfl_sync(0xffffffffu, grp.s, 0), __shfl_sync(0xffffffffu, grp.c, 0)}, 0);
+            __syncwarp();
             int buf = 0;
             for (uint64_t t = lo; t < hi; ++t) {
-                if (t + 1 < hi) bases(t + 1, buf ^ 1);   // overlaps this tile's rows
+                if (t + 1 < hi) {
+                    if (t + 1 - gfirst == 32) {
+                        gfirst = t + 1;
+                        grp = group_bases(gfirst, hi);
+                    }
+                    const int src = int(t + 1 - gfirst);
+                    row_bases(t + 1, SinCos{__shfl_sync(0xffffffffu, grp.s, src),
+                                            __shfl_sync(0xffffffffu, grp.c, src)}, buf ^ 1);
+                }
                 total = dd_add_d(total, tile_sum(t, buf));
-                __syncthreads();
+                __syncwarp();
                 buf ^= 1;
             }
         } else {
@@ -182,8 +214,8 @@ struct PartWorker {
 template <class F, class R, int MODE>
 __global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
     __shared__ Plan P;
-    __shared__ Vec2<R> sSC[2][kMaxRows];
-    __shared__ double sX0[2][kMaxRows];
+    __shared__ Vec2<R> sSC[kThreads / 32][2 * kMaxRows];   // warp-private row bases
+    __shared__ double sX0[kThreads / 32][2 * kMaxRows];
     __shared__ dd swarp[kThreads / 32];
     __shared__ __align__(16) dd sPeer[2];          // DSMEM mailbox (leader CTA), by chunk parity
     __shared__ dd sSeg[kSegments];
@@ -217,30 +249,42 @@ __global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
     }
 
     const F f = make_functor<F>(P, sTable);
-    const PartWorker<F, R, MODE> worker(P, f, sSC, sX0);
+    const PartWorker<F, R, MODE> worker(P, f, sSC[tid >> 5], sX0[tid >> 5]);
 
     const uint32_t cluster_id = blockIdx.x / csize;
     const uint32_t n_clusters = gridDim.x / csize;
 
     // ---- chunks ------------------------------------------------------------
+    // Cluster pair: CTA q takes part q of the chunk; CTA 1 drops its part sum in
+    // CTA 0's DSMEM mailbox.  The cluster barrier is split: arrive right after
+    // the store, wait only one chunk later, so neither CTA idles while its
+    // partner finishes a part that is one tile longer.
     uint32_t iter = 0;
+    bool pending = false;
+    dd pend_val{0.0, 0.0};
+    uint32_t pend_chunk = 0;
     for (uint32_t chunk = P.chunk_lo + cluster_id; chunk < P.chunk_hi; chunk += n_clusters, ++iter) {
-        dd cv;
         if (csize == 2) {
             const dd mine = block_reduce_dd(worker.run(chunk * kPartsPerChunk + crank), swarp);
+            if (pending) {
+                ptx::cluster_wait();
+                if (crank == 0 && tid == 0) st.partials[pend_chunk] = dd_add(pend_val, sPeer[(iter - 1) & 1]);
+            }
             if (crank == 1 && tid == 0)
                 ptx::st_dsmem_f64x2(ptx::mapa(&sPeer[iter & 1], 0), mine.hi, mine.lo);
-            // One cluster barrier per chunk: release of the DSMEM store, and
-            // (two iterations later) licence to overwrite the same mailbox.
-            ptx::cluster_sync_all();
-            cv = mine;
-            if (crank == 0 && tid == 0) cv = dd_add(mine, sPeer[iter & 1]);
+            ptx::cluster_arrive();
+            pending = true;
+            pend_val = mine;
+            pend_chunk = chunk;
         } else {
             const dd p0 = block_reduce_dd(worker.run(chunk * kPartsPerChunk + 0), swarp);
             const dd p1 = block_reduce_dd(worker.run(chunk * kPartsPerChunk + 1), swarp);
-            cv = dd_add(p0, p1);
+            if (tid == 0) st.partials[chunk] = dd_add(p0, p1);
         }
-        if (crank == 0 && tid == 0) st.partials[chunk] = cv;
+    }
+    if (pending) {
+        ptx::cluster_wait();
+        if (crank == 0 && tid == 0) st.partials[pend_chunk] = dd_add(pend_val, sPeer[(iter - 1) & 1]);
     }
     if (crank != 0) return;
 
