@@ -92,6 +92,8 @@ def _declare(lib, cuda):
     sig("bq_cumulative", i32, vp, P(ScanJob), vp, vp, vp, P(ScanResult))
     sig("bq_cumulative_async", i32, vp, P(ScanJob), vp, vp, vp, vp)
     sig("bq_scan_result_fetch", i32, vp, P(ScanResult))
+    sig("bq_noalloc_max_samples", u64)
+    sig("bq_cumulative_noalloc", i32, i32, P(ScanJob), vp, vp, vp, vp)
     sig("bq_ctx_export_comm", i32, vp, C.c_char_p)
     sig("bq_ctx_attach_peers", i32, vp, i32, i32, C.c_char_p)
     sig("bq_ctx_reset_comm", i32, vp)

@@ -1,0 +1,204 @@
+// bq_cumulative_noalloc: cumulative integration for callers that must not allocate.
+//
+// Who needs this: code that runs where device allocation is off the table — a
+// real-time or latency-critical loop that forbids cudaMalloc/cudaFree because
+// they synchronise the device and may take milliseconds; a plug-in living
+// inside a host application that owns all device memory and hands out only
+// fixed input/output buffers; a process running close to the memory limit
+// where an allocation can simply fail.  The regular entry points
+// (bq_cumulative, bq_ctx_create) allocate a context, a pinned staging ring and
+// scratch that grows with n; this one allocates nothing, ever.
+//
+// How: the scratch of the fused scan kernel (tile aggregates, tile prefixes,
+// segment bases, tickets, flag words, the parameter block, the result block
+// and a copy of the velocity table) lives in ONE file-scope
+// `static __device__ __align__(256)` array below.  Its size is fixed at build
+// time, which is what bounds n (BQ_NOALLOC_MAX_SAMPLES).  Every GPU that loads
+// this library carries the array (about 1.6 MB) until the process exits.
+//
+// Rules a caller has to know (also in include/b200quad.h):
+//  * The first call on a device performs the one-time set-up for that device:
+//    it resolves the array's device address with cudaGetSymbolAddress (in host
+//    code the array's name is only a host-side handle, never a device
+//    pointer), zeroes it and uploads the table.  That set-up uses synchronous
+//    runtime calls, so make the first call on each device before starting any
+//    stream capture.
+//  * All calls on a device share the one array.  Two calls that overlap on the
+//    GPU (different streams, or the same call issued again before the first
+//    finished on another stream) race on it; serialise them on one stream.
+//  * The array keeps whatever the previous call left.  The words that must
+//    start at zero (tickets, flag/generation words, barrier block, result) are
+//    cleared by a stream-ordered memset at the start of every call; the
+//    aggregate/prefix areas are fully rewritten before they are read.
+//  * Single GPU only (a world of 1): peers would need mapped memory.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "host_common.h"
+#include "scan_launch.h"
+
+namespace bq {
+namespace {
+
+constexpr uint64_t kNoAllocMaxTiles = BQ_NOALLOC_MAX_SAMPLES / kScanTile;
+static_assert(kNoAllocMaxTiles * kScanTile == BQ_NOALLOC_MAX_SAMPLES, "limit must be whole tiles");
+constexpr int kMaxDevices = 64;
+
+// Layout of the static scratch.  `control` is what a call clears up front.
+struct NoAllocControl {
+    CommBlock comm;                   // barrier words + final scalars (world of 1: local only)
+    bq_scan_result result;
+    uint64_t ready[2];                // [0] phase A -> B release word, [1] generation done
+    unsigned int ticket_a[8];
+    unsigned int ticket_b[8];
+};
+
+struct NoAllocScratch {
+    NoAllocControl control;
+    ScanPlan plan;                    // parameter block of the call in flight
+    alignas(32) double segbase[4 * kSegments];
+    alignas(32) double table[kMaxTable + 2];      // PROFILE table (default ex4vel.h values)
+    alignas(32) double agg[2 * kNoAllocMaxTiles];
+    alignas(32) double prefix[4 * kNoAllocMaxTiles];
+};
+
+// The scratch itself.  Host code must never pass this name to a kernel: see set-up below.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+struct DeviceSetup {
+    bool ready = false;
+    NoAllocScratch* scratch = nullptr;   // device address from cudaGetSymbolAddress
+    int grid = 0;
+    int table_len = 0;
+};
+
+std::mutex g_mu;
+DeviceSetup g_setup[kMaxDevices];
+
+#define BQ_NA_CUDA(expr)                                                                     \
+    do {                                                                                     \
+        cudaError_t e_ = (expr);                                                             \
+        if (e_ != cudaSuccess) {                                                             \
+            set_error("bq_cumulative_noalloc: %s failed: %s", #expr, cudaGetErrorString(e_)); \
+            return BQ_ERR_CUDA;                                                              \
+        }                                                                                    \
+    } while (0)
+
+// One-time, per device, with that device current.
+int setup_device(int device, DeviceSetup** out) {
+    std::lock_guard<std::mutex> lock(g_mu);
+    DeviceSetup& s = g_setup[device];
+    if (!s.ready) {
+        void* ptr = nullptr;
+        BQ_NA_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        NoAllocScratch* scratch = static_cast<NoAllocScratch*>(ptr);
+        BQ_NA_CUDA(cudaMemset(scratch, 0, sizeof(NoAllocScratch)));
+        int len = 0;
+        const double* table = default_profile(&len);
+        BQ_NA_CUDA(cudaMemcpy(scratch->table, table, sizeof(double) * size_t(len), cudaMemcpyHostToDevice));
+        // pad entry so the kernel's bulk copy (a multiple of 16 bytes) reads defined data
+        BQ_NA_CUDA(cudaMemcpy(scratch->table + len, table + len - 1, sizeof(double), cudaMemcpyHostToDevice));
+        int sms = 0;
+        BQ_NA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        s.grid = scan_max_grid(device, sms);
+        s.table_len = len;
+        s.scratch = scratch;
+        BQ_NA_CUDA(cudaDeviceSynchronize());
+        s.ready = true;
+    }
+    *out = &s;
+    return BQ_OK;
+}
+
+}  // namespace
+}  // namespace bq
+
+using namespace bq;
+
+extern "C" {
+
+uint64_t bq_noalloc_max_samples(void) { return BQ_NOALLOC_MAX_SAMPLES; }
+
+int bq_cumulative_noalloc(int device, const bq_scan_job* job, double* dP, double* dQ,
+                          bq_scan_result* out, void* stream) {
+    if (!job || !dP || !dQ) {
+        set_error("bq_cumulative_noalloc: job, P and Q are required");
+        return BQ_ERR_INVALID;
+    }
+    if ((uintptr_t(dP) | uintptr_t(dQ)) & 31) {
+        set_error("bq_cumulative_noalloc: P and Q must be 32-byte aligned");
+        return BQ_ERR_INVALID;
+    }
+    if (job->n > BQ_NOALLOC_MAX_SAMPLES) {
+        set_error("bq_cumulative_noalloc: n=%llu exceeds the no-allocation limit of %llu samples "
+                  "(fixed static scratch); use bq_cumulative for larger grids",
+                  (unsigned long long)job->n, (unsigned long long)BQ_NOALLOC_MAX_SAMPLES);
+        return BQ_ERR_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev || device >= kMaxDevices) {
+        cudaGetLastError();
+        set_error("bq_cumulative_noalloc: device %d not available", device);
+        return BQ_ERR_INVALID;
+    }
+    int prev = -1;
+    BQ_NA_CUDA(cudaGetDevice(&prev));
+    if (prev != device) BQ_NA_CUDA(cudaSetDevice(device));
+    struct Restore {
+        int prev, device;
+        ~Restore() {
+            if (prev >= 0 && prev != device) cudaSetDevice(prev);
+        }
+    } restore{prev, device};
+
+    DeviceSetup* s = nullptr;
+    int rc = setup_device(device, &s);
+    if (rc != BQ_OK) return rc;
+
+    ScanPlan plan;
+    rc = make_scan_plan(*job, /*rank=*/0, /*world=*/1, s->table_len, &plan);
+    if (rc != BQ_OK) return rc;
+    plan.flags = 0;   // world of 1: nothing to replicate; samples are not stored by this entry point
+    if (plan.n_tiles > kNoAllocMaxTiles) {
+        set_error("bq_cumulative_noalloc: n=%llu needs %llu tiles, the static scratch holds %llu",
+                  (unsigned long long)plan.n, (unsigned long long)plan.n_tiles,
+                  (unsigned long long)kNoAllocMaxTiles);
+        return BQ_ERR_INVALID;
+    }
+
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    NoAllocScratch* sc = s->scratch;
+    // The shared array still holds the previous call's state: zero what must start at zero.
+    BQ_NA_CUDA(cudaMemsetAsync(&sc->control, 0, sizeof(NoAllocControl), st));
+    // Parameter block: `plan` is pageable host memory, which the runtime stages
+    // before cudaMemcpyAsync returns, so the stack copy may go out of scope.
+    BQ_NA_CUDA(cudaMemcpyAsync(&sc->plan, &plan, sizeof(ScanPlan), cudaMemcpyHostToDevice, st));
+
+    ScanState state;
+    memset(&state, 0, sizeof(state));
+    state.plan = &sc->plan;
+    state.agg = sc->agg;
+    state.prefix = sc->prefix;
+    state.segbase = sc->segbase;
+    state.ready = sc->control.ready;
+    state.ticket_a = sc->control.ticket_a;
+    state.ticket_b = sc->control.ticket_b;
+    state.result = &sc->control.result;
+    state.comm = &sc->control.comm;
+    state.peers[0] = &sc->control.comm;
+    state.table = sc->table;
+    state.P = dP;
+    state.Q = dQ;
+    state.samples = nullptr;
+    unsigned grid = unsigned(s->grid);
+    if (plan.n_tiles < grid) grid = unsigned(plan.n_tiles ? plan.n_tiles : 1);
+    BQ_NA_CUDA(launch_scan(plan, state, grid, st));
+    if (out)
+        BQ_NA_CUDA(cudaMemcpyAsync(out, &sc->control.result, sizeof(bq_scan_result), cudaMemcpyDefault, st));
+    return BQ_OK;
+}
+
+}  // extern "C"

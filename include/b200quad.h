@@ -179,6 +179,32 @@ int bq_cumulative_async(bq_ctx* ctx, const bq_scan_job* job, double* dP, double*
                         double* dSamples, void* stream);
 int bq_scan_result_fetch(bq_ctx* ctx, bq_scan_result* out);
 
+/* Cumulative integration that allocates nothing (no counterpart in the
+ * reference, which cudaMallocs and frees on every run: cintegrate.cu:116-118,
+ * 143-145).  For callers that cannot allocate device memory: real-time loops
+ * where cudaMalloc/cudaFree (device-synchronising, slow) are banned, plug-ins
+ * inside a host application that owns all device memory and only lends fixed
+ * buffers, processes so close to the memory limit that an allocation may fail.
+ * Same fused kernel and same results as bq_cumulative on one GPU, but its
+ * scratch is a fixed static device array compiled into the library (about
+ * 1.6 MB per GPU, held until the process exits), so:
+ *   - n must not exceed BQ_NOALLOC_MAX_SAMPLES (larger n is rejected with
+ *     BQ_ERR_INVALID and a message; use bq_cumulative instead);
+ *   - the first call on a device does that device's one-time set-up
+ *     (synchronous runtime calls): make it before any stream capture begins;
+ *   - every call on a device shares the array: calls that overlap on the GPU
+ *     race, so issue them on one stream (or otherwise serialise them);
+ *   - single GPU only; job->replicate and job->want_samples are ignored.
+ * The caller passes the inputs (job) and the outputs: P and Q (device memory,
+ * n doubles each, 32-byte aligned) and, optionally, `out` (device or pinned
+ * host memory) which receives the result block.  Work is enqueued on `stream`
+ * (a cudaStream_t, NULL = default stream) and NOT waited for: synchronise the
+ * stream before reading P, Q or *out. */
+#define BQ_NOALLOC_MAX_SAMPLES 67108864ull     /* 32768 tiles of 2048 samples */
+uint64_t bq_noalloc_max_samples(void);
+int bq_cumulative_noalloc(int device, const bq_scan_job* job, double* dP, double* dQ,
+                          bq_scan_result* out, void* stream);
+
 /* ---- multi-GPU: peer wiring --------------------------------------------
  * Replaces MPI_Send/Recv (riemann.cpp:76,83), MPI_Reduce, MPI_Barrier and
  * MPI_Bcast (4main.c:134,137,157,200,221): the fused kernels publish their
