@@ -43,6 +43,9 @@ def parse():
     ap.add_argument("--rule", default="left")
     ap.add_argument("--dtype", default="fp64", choices=["fp64", "fp32"])
     ap.add_argument("--eval", default="auto", choices=["auto", "direct", "rotate"])
+    ap.add_argument("--combine", default="fused", choices=["fused", "nccl"],
+                    help="fused: in-kernel NVLink combine (the product); nccl: local kernel + "
+                         "torch.distributed all_reduce of one fp64 (the comparator)")
     ap.add_argument("--local-world", action="store_true",
                     help="drive --gpus GPUs from this one process instead of torchrun ranks")
     return ap.parse_args()
@@ -103,6 +106,9 @@ def main():
         if dist is not None:
             dist.barrier()
             torch.cuda.synchronize(dev)
+
+    if args.combine == "nccl":
+        return bench_nccl_comparator(args, bq, ctx, job, n, dist, dev, stream, flush, rank, world, torch)
 
     # ---- device-timed arm ---------------------------------------------------
     for _ in range(args.warmup):
@@ -178,6 +184,56 @@ def main():
             "clocks": clocks,
         }
         print(json.dumps(out))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def bench_nccl_comparator(args, bq, ctx, job, n, dist, dev, stream, flush, rank, world, torch):
+    """Baseline comparator (NOT the product path): the same kernel with its cross-GPU stage off
+    leaves this rank's segment pairs in a device buffer; torch.distributed (NCCL) all_reduces one
+    fp64 per rank.  Device-timed exactly like the fused arm."""
+    import ctypes as C
+    lib = ctx.lib
+    seg = torch.zeros(16, dtype=torch.float64, device=dev)
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+
+    def step():
+        rc = lib.bq_integrate_local_async(ctx.handle, C.byref(job), rank, world,
+                                          C.c_void_p(seg.data_ptr()), C.c_void_p(ctx.stream))
+        assert rc == 0
+        with torch.cuda.stream(stream):
+            torch.sum(seg, dim=0, keepdim=True, out=out)
+            if dist is not None:
+                dist.all_reduce(out)
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize(dev)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(args.steps)]
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    for e0, e1 in evs:
+        with torch.cuda.stream(stream):
+            flush.zero_()
+            e0.record(stream)
+        step()
+        e1.record(stream)
+    torch.cuda.synchronize(dev)
+    ms = torch.tensor([sum(e0.elapsed_time(e1) for e0, e1 in evs)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        per = float(ms) / args.steps
+        h = (job.b - job.a) / n
+        print(json.dumps({"metric": "G intervals/sec at N=2^%d, NCCL comparator" % args.log2n,
+                          "impl": "b200quad local kernel + NCCL all_reduce (comparator)",
+                          "value": n / (per * 1e-3) / 1e9, "unit": "Gintervals/s", "n_gpus": args.gpus,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": per,
+                          "higher_is_better": True, "scaling": "strong", "dtype": args.dtype,
+                          "result": float(out) * h, "gpu_launches": args.steps * args.gpus}))
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
