@@ -27,6 +27,16 @@ static dd butterfly(dd* v, int lanes) {
     return v[0];
 }
 
+// warp_reduce_lazy(): same shape, un-normalised pairs.
+static dd butterfly_lazy(dd* v, int lanes) {
+    dd tmp[32];
+    for (int off = lanes / 2; off >= 1; off >>= 1) {
+        for (int l = 0; l < lanes; ++l) tmp[l] = dd_add_lazy(v[l], v[l ^ off]);
+        for (int l = 0; l < lanes; ++l) v[l] = tmp[l];
+    }
+    return v[0];
+}
+
 template <class F, class R>
 struct CpuWorker {
     const Plan& P;
@@ -73,7 +83,8 @@ struct CpuWorker {
         uint64_t lo, hi;
         part_tiles(P, part_idx, lo, hi);
         dd total[kThreads];
-        for (int t = 0; t < kThreads; ++t) total[t] = dd{0.0, 0.0};
+        TileAcc<R> accs[kThreads];
+        for (int t = 0; t < kThreads; ++t) total[t] = dd{0.0, 0.0}, accs[t].clear();
         R S[kMaxRows], C[kMaxRows];
         double X0[kMaxRows];
         for (uint64_t tile = lo; tile < hi; ++tile) {
@@ -92,8 +103,7 @@ struct CpuWorker {
                 const R* cjt = &cj[t * kCols];
                 const R* sjt = &sj[t * kCols];
                 const double* dxt = &dx[t * kCols];
-                TileAcc<R> acc;
-                acc.clear();
+                TileAcc<R>& acc = accs[t];
                 double rb = row_base_index(P, g, 0);
                 for (uint32_t r = 0; r < g.full_rows; ++r) {
                     R v[kCols];
@@ -111,13 +121,16 @@ struct CpuWorker {
                                                                        X0[r], dxt[j])
                                                   : point_direct<F, R>(f, rb, dxt[j], P.h, P.a));
                 }
-                total[t] = dd_add_d(total[t], acc.flush());
+                if (((tile - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || tile + 1 == hi) {
+                    total[t] = dd_acc_lazy(total[t], acc.flush());
+                    acc.clear();
+                }
             }
         }
-        // block_reduce_dd(): 8 warp butterflies, then an 8-lane butterfly.
+        // block_reduce_dd(): 8 warp butterflies, then an 8-lane butterfly, one renormalisation.
         dd wsum[8];
-        for (int w = 0; w < kThreads / 32; ++w) wsum[w] = butterfly(&total[w * 32], 32);
-        return butterfly(wsum, 8);
+        for (int w = 0; w < kThreads / 32; ++w) wsum[w] = butterfly_lazy(&total[w * 32], 32);
+        return dd_renorm(butterfly_lazy(wsum, 8));
     }
 
     dd chunk(uint32_t c) const {

@@ -30,6 +30,7 @@ constexpr int kThreads = 256;                 // threads per CTA (fixed: part of
 constexpr int kCols = 8;                      // columns per thread
 constexpr int kWidth = kThreads * kCols;      // points per row
 constexpr int kMaxRows = 32;                  // rows per tile upper bound (one per lane)
+constexpr int kFlushTiles = 4;                 // tiles a thread sums before a compensated flush
 constexpr int kPartsPerChunk = 2;             // == cluster size when clusters are on
 constexpr int kChunks = 2368;                 // 8 segments x 296 chunks (= 16 x 148 SMs)
 constexpr int kParts = kChunks * kPartsPerChunk;

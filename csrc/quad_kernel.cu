@@ -46,18 +46,25 @@ __device__ __forceinline__ dd warp_reduce_dd(dd v) {
     for (int off = 16; off >= 1; off >>= 1) v = dd_add(v, shfl_xor_dd(v, off));
     return v;
 }
+// Same shape with un-normalised pairs (shorter dependent chain); see bq_dd.cuh.
+__device__ __forceinline__ dd warp_reduce_lazy(dd v) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v = dd_add_lazy(v, shfl_xor_dd(v, off));
+    return v;
+}
 
 // CTA-wide dd reduction; the result is valid in warp 0 (all lanes).
 __device__ __forceinline__ dd block_reduce_dd(dd v, dd* swarp) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    v = warp_reduce_dd(v);
+    v = warp_reduce_lazy(v);
     if (lane == 0) swarp[warp] = v;
     __syncthreads();
     dd r{0.0, 0.0};
     if (warp == 0) {
         r = lane < kThreads / 32 ? swarp[lane] : dd{0.0, 0.0};
 #pragma unroll
-        for (int off = 4; off >= 1; off >>= 1) r = dd_add(r, shfl_xor_dd(r, off));
+        for (int off = 4; off >= 1; off >>= 1) r = dd_add_lazy(r, shfl_xor_dd(r, off));
+        r = dd_renorm(r);
     }
     __syncthreads();
     return r;
@@ -72,13 +79,16 @@ struct PartWorker {
     Vec2<R>* wSC;         // this warp's private row bases: [2][kMaxRows]
     double* wX0;          // this warp's private row x0:    [2][kMaxRows]
     const double h, a;    // register copies for the hot loops
+    const uint32_t rows;  // rows of every tile but the last
+    const uint64_t last_tile, tile_pts;
     // column constants
     R cj[kCols], sj[kCols];
     double dx[kCols];     // ROTATE: x offset of the column; DIRECT: column index as double
     SinCos rowrot;        // ROTATE: rotation of row `lane` relative to the tile base
 
     __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R>* sc, double* x0)
-        : P(P_), f(f_), wSC(sc), wX0(x0), h(P_.h), a(P_.a) {
+        : P(P_), f(f_), wSC(sc), wX0(x0), h(P_.h), a(P_.a), rows(P_.rows),
+          last_tile(P_.n_tiles - 1), tile_pts(P_.tile_pts) {
         const int lane = threadIdx.x & 31;
         if (kRotate) {
             // Two sincos per thread for all kCols columns: the thread's own
@@ -113,7 +123,7 @@ struct PartWorker {
         const uint64_t tile = first + (threadIdx.x & 31);
         SinCos g{0.0, 1.0};
         if (tile < hi) {
-            const double xt = fma(double(tile * P.tile_pts) + P.off, h, a);
+            const double xt = fma(double(tile * tile_pts) + P.off, h, a);
             sincos(f.angle(xt), &g.s, &g.c);
         }
         return g;
@@ -125,16 +135,21 @@ struct PartWorker {
         const int lane = threadIdx.x & 31;
         const SinCos rb = rotate_sc(tb, rowrot);
         wSC[buf * kMaxRows + lane] = Vec2<R>{R(rb.s), R(rb.c)};
-        if (F::kNeedX) {
-            const TileGeom g = tile_geom(P, tile);
-            wX0[buf * kMaxRows + lane] = fma(row_base_index(P, g, lane), h, a);
-        }
+        if (F::kNeedX)
+            wX0[buf * kMaxRows + lane] =
+                fma(double(tile * tile_pts + uint64_t(lane) * kWidth) + P.off, h, a);
     }
 
-    __device__ __forceinline__ double tile_sum(uint64_t tile, int buf) const {
-        const TileGeom g = tile_geom(P, tile);
-        TileAcc<R> acc;
-        acc.clear();
+    // Adds every sample of `tile` into `acc`.  Only the globally last tile can be short.
+    __device__ __forceinline__ void tile_accumulate(uint64_t tile, int buf, TileAcc<R>& acc) const {
+        TileGeom g;
+        if (tile == last_tile) {
+            g = tile_geom(P, tile);
+        } else {
+            g.start = tile * tile_pts;
+            g.full_rows = rows;
+            g.rem = 0;
+        }
         if (kRotate) {
             const Vec2<R>* sc_row = wSC + buf * kMaxRows;
             const double* x0_row = wX0 + buf * kMaxRows;
@@ -173,7 +188,6 @@ struct PartWorker {
                         acc.add_one(j, point_direct<F, R>(f, rb, dx[j], h, a));
             }
         }
-        return acc.flush();
     }
 
     // All tiles of one part; returns this thread's dd total.  In ROTATE mode a
@@ -183,6 +197,8 @@ struct PartWorker {
         uint64_t lo, hi;
         part_tiles(P, part, lo, hi);
         dd total{0.0, 0.0};
+        TileAcc<R> acc;
+        acc.clear();
         if (kRotate) {
             if (lo >= hi) return total;
             uint64_t gfirst = lo;
@@ -200,14 +216,24 @@ struct PartWorker {
                     row_bases(t + 1, SinCos{__shfl_sync(0xffffffffu, grp.s, src),
                                             __shfl_sync(0xffffffffu, grp.c, src)}, buf ^ 1);
                 }
-                total = dd_add_d(total, tile_sum(t, buf));
+                tile_accumulate(t, buf, acc);
+                if (((t - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || t + 1 == hi) {
+                    total = dd_acc_lazy(total, acc.flush());
+                    acc.clear();
+                }
                 __syncwarp();
                 buf ^= 1;
             }
         } else {
-            for (uint64_t t = lo; t < hi; ++t) total = dd_add_d(total, tile_sum(t, 0));
+            for (uint64_t t = lo; t < hi; ++t) {
+                tile_accumulate(t, 0, acc);
+                if (((t - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || t + 1 == hi) {
+                    total = dd_acc_lazy(total, acc.flush());
+                    acc.clear();
+                }
+            }
         }
-        return total;
+        return total;   // un-normalised; block_reduce_dd() renormalises
     }
 };
 
@@ -263,7 +289,16 @@ __global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
     bool pending = false;
     dd pend_val{0.0, 0.0};
     uint32_t pend_chunk = 0;
-    for (uint32_t chunk = P.chunk_lo + cluster_id; chunk < P.chunk_hi; chunk += n_clusters, ++iter) {
+    for (uint32_t chunk = P.chunk_lo + cluster_id; chunk < P.chunk_hi; chunk += n_clusters) {
+        {   // Small n leaves most chunks without a tile: no reduction, no barrier for those.
+            uint64_t lo0, hi0, lo1, hi1;
+            part_tiles(P, chunk * kPartsPerChunk, lo0, hi0);
+            part_tiles(P, chunk * kPartsPerChunk + 1, lo1, hi1);
+            if (lo0 >= hi1) {
+                if (crank == 0 && tid == 0) st.partials[chunk] = dd{0.0, 0.0};
+                continue;
+            }
+        }
         if (csize == 2) {
             const dd mine = block_reduce_dd(worker.run(chunk * kPartsPerChunk + crank), swarp);
             if (pending) {
@@ -276,6 +311,7 @@ __global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
             pending = true;
             pend_val = mine;
             pend_chunk = chunk;
+            ++iter;
         } else {
             const dd p0 = block_reduce_dd(worker.run(chunk * kPartsPerChunk + 0), swarp);
             const dd p1 = block_reduce_dd(worker.run(chunk * kPartsPerChunk + 1), swarp);
