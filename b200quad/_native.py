@@ -109,6 +109,8 @@ def _declare(lib, cuda):
     sig("bq_world_cumulative", i32, vp, P(ScanJob), P(vp), P(vp), P(ScanResult))
     sig("bq_integrate_local_async", i32, vp, P(Job), i32, i32, vp, vp)
     sig("bq_ctx_inject_fault", i32, vp, i32)
+    sig("bq_ctx_trace", i32, vp, i32)
+    sig("bq_ctx_trace_read", i32, vp, P(u64), i32)
 
 
 class NativeError(RuntimeError):

@@ -87,6 +87,15 @@ class Context:
     def inject_fault(self, kind=1):
         check(self.lib.bq_ctx_inject_fault(self.handle, int(kind)), "bq_ctx_inject_fault")
 
+    def trace(self, enable=True):
+        """Per-CTA timeline of the quad kernel (start ns, end ns, SM id, tiles)."""
+        check(self.lib.bq_ctx_trace(self.handle, 1 if enable else 0), "bq_ctx_trace")
+
+    def read_trace(self):
+        buf = (C.c_uint64 * (4 * 4096))()
+        n = self.lib.bq_ctx_trace_read(self.handle, buf, 4096)
+        return [tuple(buf[4 * i + k] for k in range(4)) for i in range(n)]
+
     def reset_comm(self):
         check(self.lib.bq_ctx_reset_comm(self.handle), "bq_ctx_reset_comm")
 

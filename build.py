@@ -26,7 +26,7 @@ BINDIR = os.path.join(ROOT, "bin")
 NVCC = os.environ.get("NVCC", shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("CXX", "g++")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC", "-Xptxas", "-v"] + ARCH
+NVCC_FLAGS = os.environ.get("BQ_NVCC_EXTRA", "").split() + ["-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC", "-Xptxas", "-v"] + ARCH
 CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-Wall", "-Wno-unknown-pragmas",
              "-Wno-unused-function"]
 
@@ -64,7 +64,7 @@ def _headers():
 def _compile(src, out, cmd_prefix, stamp_extra, force, log):
     """Compile src -> out unless a stamp says inputs are unchanged."""
     stamp = out + ".stamp"
-    want = _digest([src] + _headers(), stamp_extra)
+    want = _digest([src] + _headers(), stamp_extra + os.environ.get("BQ_NVCC_EXTRA", ""))
     if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == want:
         return False
     _run(cmd_prefix + ["-c", src, "-o", out], log)

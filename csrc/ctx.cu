@@ -127,6 +127,7 @@ void bq_ctx_destroy(bq_ctx* c) {
     cudaFree(c->d_comm);
     cudaFree(c->d_table);
     cudaFree(c->d_seg_scratch);
+    cudaFree(c->d_trace);
     cudaFreeHost(c->h_plans);
     cudaFreeHost(c->h_result);
     cudaFreeHost(c->h_scan_result);
@@ -174,6 +175,31 @@ int bq_ctx_set_timeout_ms(bq_ctx* c, int ms) {
     if (!c || ms < 1) return BQ_ERR_INVALID;
     c->timeout_ms = uint32_t(ms);
     return BQ_OK;
+}
+
+// Per-CTA timeline of the quad kernel: (start ns, end ns, smid, tiles) per CTA.
+int bq_ctx_trace(bq_ctx* c, int enable) {
+    if (!c) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    BQ_CUDA(cudaStreamSynchronize(c->stream));
+    if (enable && !c->d_trace) {
+        BQ_CUDA(cudaMalloc(&c->d_trace, sizeof(uint64_t) * 4 * 4096));
+        BQ_CUDA(cudaMemset(c->d_trace, 0, sizeof(uint64_t) * 4 * 4096));
+    } else if (!enable && c->d_trace) {
+        BQ_CUDA(cudaFree(c->d_trace));
+        c->d_trace = nullptr;
+    }
+    return BQ_OK;
+}
+
+int bq_ctx_trace_read(bq_ctx* c, uint64_t* out, int max_ctas) {
+    if (!c || !out || !c->d_trace) return 0;
+    DeviceGuard guard(c->device);
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess) return 0;
+    int n = c->trace_ctas < max_ctas ? c->trace_ctas : max_ctas;
+    if (cudaMemcpy(out, c->d_trace, sizeof(uint64_t) * 4 * size_t(n), cudaMemcpyDeviceToHost) != cudaSuccess)
+        return 0;
+    return n;
 }
 
 int bq_ctx_inject_fault(bq_ctx* c, int kind) {
@@ -246,6 +272,8 @@ static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint3
     st.peers[rank] = c->d_comm;
     st.table = c->d_table;
     st.seg_out = seg_out;
+    st.trace = c->d_trace;
+    c->trace_ctas = c->d_trace ? int(quad_config(c).grid) : 0;
     BQ_CUDA(launch_quad(*hp, st, quad_config(c), stream));
     c->launches += 1;
     BQ_CUDA(cudaMemcpyAsync(c->h_result, c->d_result, sizeof(bq_result), cudaMemcpyDeviceToHost,

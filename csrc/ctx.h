@@ -48,6 +48,8 @@ struct bq_ctx {
     bq::CommBlock* d_comm = nullptr;
     double* d_table = nullptr;
     double* d_seg_scratch = nullptr;
+    uint64_t* d_trace = nullptr;          // per-CTA timeline, allocated by bq_ctx_trace(on)
+    int trace_ctas = 0;
     int table_len = 0;
     std::vector<double> h_table;
 

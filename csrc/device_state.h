@@ -31,6 +31,7 @@ struct DeviceState {
     CommBlock* peers[BQ_MAX_WORLD];   // comm block of rank r as mapped here
     const double* table;      // PROFILE table (padded to an even count)
     double* seg_out;          // kFlagLocalOnly: 2*kSegments doubles, else null
+    uint64_t* trace;          // optional per-CTA timeline: [cta](start ns, end ns, smid, tiles)
 };
 
 }  // namespace bq

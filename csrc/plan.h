@@ -32,7 +32,7 @@ constexpr int kWidth = kThreads * kCols;      // points per row
 constexpr int kMaxRows = 32;                  // rows per tile upper bound (one per lane)
 constexpr int kFlushTiles = 4;                 // tiles a thread sums before a compensated flush
 constexpr int kPartsPerChunk = 2;             // == cluster size when clusters are on
-constexpr int kChunks = 2368;                 // 8 segments x 296 chunks (= 16 x 148 SMs)
+constexpr int kChunks = 1184;                 // 8 segments x 148 chunks: one per cluster on 8 GPUs
 constexpr int kParts = kChunks * kPartsPerChunk;
 constexpr int kSegments = BQ_SEGMENTS;
 constexpr int kChunksPerSegment = kChunks / kSegments;

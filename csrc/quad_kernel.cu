@@ -23,6 +23,10 @@
 #include "quad_core.cuh"
 #include "quad_launch.h"
 
+#ifndef BQ_MIN_CTAS
+#define BQ_MIN_CTAS 2
+#endif
+
 namespace bq {
 
 template <class R>
@@ -153,19 +157,23 @@ struct PartWorker {
         if (kRotate) {
             const Vec2<R>* sc_row = wSC + buf * kMaxRows;
             const double* x0_row = wX0 + buf * kMaxRows;
+            // Software-pipelined: the next row's base is in flight while this row's
+            // 24 fp64 instructions issue (index full_rows is a valid slot).
+            Vec2<R> sc = sc_row[0];
+            double x0 = F::kNeedX ? x0_row[0] : 0.0;
 #pragma unroll 4
             for (uint32_t r = 0; r < g.full_rows; ++r) {
-                const Vec2<R> sc = sc_row[r];
-                const double x0 = F::kNeedX ? x0_row[r] : 0.0;
+                const Vec2<R> sc_next = sc_row[r + 1];
+                const double x0_next = F::kNeedX ? x0_row[r + 1] : 0.0;
                 R v[kCols];
 #pragma unroll
                 for (int j = 0; j < kCols; ++j)
                     v[j] = point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]);
                 acc.add_row(v);
+                sc = sc_next;
+                x0 = x0_next;
             }
-            if (g.rem) {
-                const Vec2<R> sc = sc_row[g.full_rows];
-                const double x0 = F::kNeedX ? x0_row[g.full_rows] : 0.0;
+            if (g.rem) {   // sc / x0 already hold row full_rows
 #pragma unroll
                 for (int j = 0; j < kCols; ++j)
                     if (threadIdx.x + kThreads * j < g.rem)
@@ -238,10 +246,10 @@ struct PartWorker {
 };
 
 template <class F, class R, int MODE>
-__global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
+__global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(DeviceState st) {
     __shared__ Plan P;
-    __shared__ Vec2<R> sSC[kThreads / 32][2 * kMaxRows];   // warp-private row bases
-    __shared__ double sX0[kThreads / 32][2 * kMaxRows];
+    __shared__ Vec2<R> sSC[kThreads / 32][2 * kMaxRows + 2];   // warp-private row bases (+pad)
+    __shared__ double sX0[kThreads / 32][2 * kMaxRows + 2];
     __shared__ dd swarp[kThreads / 32];
     __shared__ __align__(16) dd sPeer[2];          // DSMEM mailbox (leader CTA), by chunk parity
     __shared__ dd sSeg[kSegments];
@@ -255,6 +263,8 @@ __global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
     const uint32_t csize = ptx::cluster_nctarank();
 
     if (blockIdx.x == 0 && tid == 0) st.result->t_start_ns = ptx::globaltimer();
+    uint64_t trace_t0 = 0, trace_tiles = 0;
+    if (st.trace && tid == 0) trace_t0 = ptx::globaltimer();
 
     // ---- plan (+ table) into shared memory ---------------------------------
     {
@@ -289,11 +299,18 @@ __global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
     bool pending = false;
     dd pend_val{0.0, 0.0};
     uint32_t pend_chunk = 0;
-    for (uint32_t chunk = P.chunk_lo + cluster_id; chunk < P.chunk_hi; chunk += n_clusters) {
+    // A cluster owns a contiguous run of chunks: for small n the few chunks that
+    // hold a tile are evenly spaced, and a strided assignment would pile them
+    // all onto the same handful of clusters.
+    const uint32_t per_cluster = (P.chunk_hi - P.chunk_lo + n_clusters - 1) / n_clusters;
+    const uint32_t my_lo = P.chunk_lo + cluster_id * per_cluster;
+    const uint32_t my_hi = my_lo + per_cluster < P.chunk_hi ? my_lo + per_cluster : P.chunk_hi;
+    for (uint32_t chunk = my_lo; chunk < my_hi; ++chunk) {
         {   // Small n leaves most chunks without a tile: no reduction, no barrier for those.
             uint64_t lo0, hi0, lo1, hi1;
             part_tiles(P, chunk * kPartsPerChunk, lo0, hi0);
             part_tiles(P, chunk * kPartsPerChunk + 1, lo1, hi1);
+            if (st.trace) trace_tiles += (csize == 2) ? (crank ? hi1 - lo1 : hi0 - lo0) : hi1 - lo0;
             if (lo0 >= hi1) {
                 if (crank == 0 && tid == 0) st.partials[chunk] = dd{0.0, 0.0};
                 continue;
@@ -321,6 +338,12 @@ __global__ void __launch_bounds__(kThreads, 2) quad_kernel(DeviceState st) {
     if (pending) {
         ptx::cluster_wait();
         if (crank == 0 && tid == 0) st.partials[pend_chunk] = dd_add(pend_val, sPeer[(iter - 1) & 1]);
+    }
+    if (st.trace && tid == 0) {
+        uint32_t smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        uint64_t* t = st.trace + 4 * blockIdx.x;
+        t[0] = trace_t0, t[1] = ptx::globaltimer(), t[2] = smid, t[3] = trace_tiles;
     }
     if (crank != 0) return;
 

@@ -248,6 +248,13 @@ int bq_device_alloc(int device, size_t bytes, void** out);
 int bq_device_free(int device, void* p);
 int bq_device_read(int device, void* host_dst, const void* dev_src, size_t bytes);
 
+/* Tracing: when enabled every CTA of the quad kernel records (start ns, end ns,
+ * SM id, tiles processed) from %globaltimer; read back after a call.  The
+ * reference's only instrumentation is one wall-clock pair around main()
+ * (riemann.cpp:51,91; cintegrate.cu:104,139). */
+int bq_ctx_trace(bq_ctx* ctx, int enable);
+int bq_ctx_trace_read(bq_ctx* ctx, uint64_t* out /* 4 per CTA */, int max_ctas);
+
 /* Fault injection for the time-out path: the next launch on this context
  * skips its publish step (its peers must report BQ_ERR_TIMEOUT). */
 int bq_ctx_inject_fault(bq_ctx* ctx, int kind);
