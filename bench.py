@@ -53,12 +53,32 @@ def parse():
 
 def run_reference(args):
     from baseline import reference_arm
-    print(json.dumps(reference_arm.run(args.gpus, args.steps, args.warmup)))
+    if int(os.environ.get("RANK", "0")) == 0:
+        emit(reference_arm.run(args.gpus, args.steps, args.warmup))
     return 0
+
+
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """Everything except the final JSON line goes to stderr: libraries (NCCL's version banner,
+    torchrun) write to fd 1 behind Python's back, and the driver wants exactly one line."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(obj):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(obj) + "\n")
+    out.flush()
 
 
 def main():
     args = parse()
+    _quiet_stdout()
     if args.impl == "reference":
         return run_reference(args)
 
@@ -183,7 +203,7 @@ def main():
             "rel_err_vs_oracle": abs(last.value - exact) / abs(exact) if exact else None,
             "clocks": clocks,
         }
-        print(json.dumps(out))
+        emit(out)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -228,12 +248,12 @@ def bench_nccl_comparator(args, bq, ctx, job, n, dist, dev, stream, flush, rank,
     if rank == 0:
         per = float(ms) / args.steps
         h = (job.b - job.a) / n
-        print(json.dumps({"metric": "G intervals/sec at N=2^%d, NCCL comparator" % args.log2n,
+        emit({"metric": "G intervals/sec at N=2^%d, NCCL comparator" % args.log2n,
                           "impl": "b200quad local kernel + NCCL all_reduce (comparator)",
                           "value": n / (per * 1e-3) / 1e9, "unit": "Gintervals/s", "n_gpus": args.gpus,
                           "steps": args.steps, "warmup": args.warmup, "ms_per_step": per,
                           "higher_is_better": True, "scaling": "strong", "dtype": args.dtype,
-                          "result": float(out) * h, "gpu_launches": args.steps * args.gpus}))
+                          "result": float(out) * h, "gpu_launches": args.steps * args.gpus})
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -267,7 +287,7 @@ def bench_local_world(args, bq, parallel, job, n, torch):
         t_wall += time.perf_counter() - t0
         ms += max(float(r.device_ms) for r in res)
     value = n / (ms / args.steps * 1e-3) / 1e9
-    print(json.dumps({
+    emit({
         "metric": "G intervals/sec at N=2^%d (time-to-solution = ms_per_step)" % args.log2n,
         "value": value, "unit": "Gintervals/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -279,7 +299,7 @@ def bench_local_world(args, bq, parallel, job, n, torch):
         "e2e": {"value": n / (t_wall / args.steps) / 1e9, "unit": "Gintervals/s",
                 "h2d_bytes_per_step": bytes_h2d() * args.gpus,
                 "d2h_bytes_per_step": bytes_d2h() * args.gpus},
-        "gpu_launches": args.steps * args.gpus, "result": float(res[0].value)}))
+        "gpu_launches": args.steps * args.gpus, "result": float(res[0].value)})
     return 0
 
 
