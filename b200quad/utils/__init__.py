@@ -3,6 +3,7 @@ import ctypes as C
 import json
 import math
 import subprocess
+import os
 import threading
 import time
 
@@ -39,20 +40,62 @@ def oracle_profile(n, a=0.0, b=1800.0, rule="left", table=None):
 
 
 class ClockSampler:
-    """Samples nvidia-smi SM clocks and throttle reasons while a timed region runs."""
+    """Samples SM clocks, power and throttle reasons while a timed region runs.
+
+    NVML (the library nvidia-smi itself reads) is polled in-process every few
+    milliseconds, so even a sub-second timed region collects a useful number of
+    samples; if the NVML binding is missing, `nvidia-smi` is spawned instead.
+    """
 
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index=0, period_ms=100):
+    def __init__(self, gpu_index=0, period_ms=5):
         self.gpu_index = gpu_index
         self.period = period_ms / 1000.0
         self.samples = []
+        self.source = None
         self._stop = threading.Event()
         self._thr = None
 
+    def _nvml_handle(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            idx = self.gpu_index
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            if vis:
+                try:
+                    idx = int(vis.split(",")[self.gpu_index])
+                except (ValueError, IndexError):
+                    idx = self.gpu_index
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(idx)
+        except Exception:
+            return None, None
+
     def _poll(self):
+        nv, h = self._nvml_handle()
+        if h is not None:
+            self.source = "nvml"
+            R = nv
+            bits = [("hw_slowdown", getattr(R, "nvmlClocksThrottleReasonHwSlowdown", 0x8)),
+                    ("hw_thermal_slowdown", getattr(R, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40)),
+                    ("sw_thermal_slowdown", getattr(R, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20)),
+                    ("sw_power_cap", getattr(R, "nvmlClocksThrottleReasonSwPowerCap", 0x4))]
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            while not self._stop.is_set():
+                try:
+                    sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                    pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    self.samples.append([str(sm), str(mx), str(pw)] +
+                                        ["Active" if mask & b else "Not Active" for _, b in bits])
+                except Exception:
+                    pass
+                self._stop.wait(self.period)
+            return
+        self.source = "nvidia-smi"
         while not self._stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.gpu_index),
@@ -92,7 +135,7 @@ class ClockSampler:
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "power_w_max": max(power) if power else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": self.source}
 
 
 def json_line(**kw):

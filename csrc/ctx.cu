@@ -90,7 +90,8 @@ int bq_ctx_create(int device, bq_ctx** out) {
     BQ_CUDA(cudaMalloc(&c->d_seg_scratch, sizeof(double) * 2 * kSegments));
 
     BQ_CUDA(cudaHostAlloc(&c->h_plans, sizeof(PlanSlot) * kRing, cudaHostAllocDefault));
-    BQ_CUDA(cudaHostAlloc(&c->h_result, sizeof(bq_result), cudaHostAllocDefault));
+    BQ_CUDA(cudaHostAlloc(&c->h_result, sizeof(bq_result), cudaHostAllocMapped));
+    BQ_CUDA(cudaHostGetDevicePointer((void**)&c->h_result_dev, c->h_result, 0));
     BQ_CUDA(cudaHostAlloc(&c->h_scan_result, sizeof(bq_scan_result), cudaHostAllocDefault));
     memset(c->h_result, 0, sizeof(bq_result));
     memset(c->h_scan_result, 0, sizeof(bq_scan_result));
@@ -230,11 +231,15 @@ int ring_release(bq_ctx* c, int slot, cudaStream_t stream) {
     return BQ_OK;
 }
 
-static LaunchConfig quad_config(const bq_ctx* c) {
+static LaunchConfig quad_config(const bq_ctx* c, const Plan& P) {
     LaunchConfig cfg;
     cfg.cluster = unsigned(c->cluster);
     unsigned grid = unsigned(c->sm_count * c->ctas_per_sm);
-    grid -= grid % cfg.cluster;
+    // Small n: this rank holds only a few tiles, so launch only as many CTAs as
+    // get one each (the grid shape never changes the result, see plan.h).
+    const uint64_t my_tiles = (P.n_tiles + uint64_t(P.world) - 1) / uint64_t(P.world);
+    if (my_tiles < grid) grid = unsigned(my_tiles ? my_tiles : 1);
+    grid += (cfg.cluster - grid % cfg.cluster) % cfg.cluster;
     if (grid < cfg.cluster) grid = cfg.cluster;
     cfg.grid = grid;
     return cfg;
@@ -242,11 +247,10 @@ static LaunchConfig quad_config(const bq_ctx* c) {
 
 static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint32_t extra_flags,
                         double* seg_out, cudaStream_t stream) {
-    int slot = 0;
-    int rc = ring_acquire(c, &slot);
-    if (rc != BQ_OK) return rc;
-    Plan* hp = &c->h_plans[slot].quad;
-    rc = make_plan(*job, rank, world, c->rows_override, c->table_len, hp);
+    // The plan travels in the kernel parameter buffer: no staging copy.
+    Plan plan;
+    Plan* hp = &plan;
+    int rc = make_plan(*job, rank, world, c->rows_override, c->table_len, hp);
     if (rc != BQ_OK) return rc;
     hp->flags = extra_flags | c->fault_flags;
     c->fault_flags = 0;
@@ -258,28 +262,24 @@ static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint3
                 return BQ_ERR_INVALID;
             }
     }
-    Plan* dp = &c->d_plans[slot].quad;
-    BQ_CUDA(cudaMemcpyAsync(dp, hp, sizeof(Plan), cudaMemcpyHostToDevice, stream));
 
     DeviceState st;
     memset(&st, 0, sizeof(st));
-    st.plan = dp;
     st.partials = c->d_partials;
     st.ticket = c->d_ticket;
     st.result = c->d_result;
+    st.result_host = c->h_result_dev;   // the kernel itself writes the result block to the host
     st.comm = c->d_comm;
     for (int r = 0; r < BQ_MAX_WORLD; ++r) st.peers[r] = c->peers[r];
     st.peers[rank] = c->d_comm;
     st.table = c->d_table;
     st.seg_out = seg_out;
     st.trace = c->d_trace;
-    c->trace_ctas = c->d_trace ? int(quad_config(c).grid) : 0;
-    BQ_CUDA(launch_quad(*hp, st, quad_config(c), stream));
+    c->trace_ctas = c->d_trace ? int(quad_config(c, *hp).grid) : 0;
+    BQ_CUDA(launch_quad(*hp, st, quad_config(c, *hp), stream));
     c->launches += 1;
-    BQ_CUDA(cudaMemcpyAsync(c->h_result, c->d_result, sizeof(bq_result), cudaMemcpyDeviceToHost,
-                            stream));
     c->last_stream = stream;
-    return ring_release(c, slot, stream);
+    return BQ_OK;
 }
 
 }  // namespace bq

@@ -65,6 +65,7 @@ struct bq_ctx {
     // pinned staging
     bq::PlanSlot* h_plans = nullptr;
     bq_result* h_result = nullptr;
+    bq_result* h_result_dev = nullptr;    // h_result as the device addresses it (mapped)
     bq_scan_result* h_scan_result = nullptr;
     cudaEvent_t ring_ev[bq::kRing];
     bool ring_busy[bq::kRing];

@@ -23,10 +23,10 @@ struct alignas(256) CommBlock {
 };
 
 struct DeviceState {
-    const Plan* plan;         // device copy of the plan (H2D per call)
     dd* partials;             // [kChunks] chunk sums
     unsigned int* ticket;     // clusters finished (reset by the last one)
     bq_result* result;        // device result block
+    bq_result* result_host;   // pinned host result block as mapped on this device (or null)
     CommBlock* comm;          // own comm block
     CommBlock* peers[BQ_MAX_WORLD];   // comm block of rank r as mapped here
     const double* table;      // PROFILE table (padded to an even count)

@@ -1,8 +1,10 @@
 // The fused definite-integral kernel: ONE launch per GPU per integrate() call.
 //
-//   evaluate f on this rank's share of the n sample points        (hot loop)
-//   -> per-thread dd totals -> warp shuffle -> CTA (smem)
-//   -> thread-block cluster pair through DSMEM                     (chunk sum)
+//   evaluate f on this rank's share of the n sample points        (hot loop,
+//      no CTA-wide or cluster-wide synchronisation inside it)
+//   -> per-thread dd totals -> warp shuffle -> per-warp part totals in smem
+//   -> once per CTA: cross-warp combine, then the thread-block cluster pair
+//      exchanges its part sums through DSMEM                       (chunk sums)
 //   -> ticket; the last cluster folds chunk sums into segment sums
 //   -> publish segment pairs into every peer's comm block over NVLink,
 //      in-kernel epoch barrier, fixed-order fold, *h, rule epilogue -> result
@@ -55,23 +57,6 @@ __device__ __forceinline__ dd warp_reduce_lazy(dd v) {
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) v = dd_add_lazy(v, shfl_xor_dd(v, off));
     return v;
-}
-
-// CTA-wide dd reduction; the result is valid in warp 0 (all lanes).
-__device__ __forceinline__ dd block_reduce_dd(dd v, dd* swarp) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    v = warp_reduce_lazy(v);
-    if (lane == 0) swarp[warp] = v;
-    __syncthreads();
-    dd r{0.0, 0.0};
-    if (warp == 0) {
-        r = lane < kThreads / 32 ? swarp[lane] : dd{0.0, 0.0};
-#pragma unroll
-        for (int off = 4; off >= 1; off >>= 1) r = dd_add_lazy(r, shfl_xor_dd(r, off));
-        r = dd_renorm(r);
-    }
-    __syncthreads();
-    return r;
 }
 
 template <class F, class R, int MODE>
@@ -241,17 +226,29 @@ struct PartWorker {
                 }
             }
         }
-        return total;   // un-normalised; block_reduce_dd() renormalises
+        return total;   // un-normalised; renormalised once per part after the cross-warp combine
     }
 };
 
+// Parts a CTA reduces in one go: its share of up to kBatchChunks chunks
+// (one part per chunk when a cluster pair splits the chunk, else both).
+constexpr int kBatchChunks = 8;
+constexpr int kBatchSlots = kBatchChunks * kPartsPerChunk;
+
+struct QuadParams {
+    Plan P;            // 152 bytes, rides in the kernel parameter buffer
+    DeviceState st;
+};
+
 template <class F, class R, int MODE>
-__global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(DeviceState st) {
-    __shared__ Plan P;
+__global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __grid_constant__ QuadParams prm) {
+    const Plan& P = prm.P;
+    const DeviceState& st = prm.st;
     __shared__ Vec2<R> sSC[kThreads / 32][2 * kMaxRows + 2];   // warp-private row bases (+pad)
     __shared__ double sX0[kThreads / 32][2 * kMaxRows + 2];
-    __shared__ dd swarp[kThreads / 32];
-    __shared__ __align__(16) dd sPeer[2];          // DSMEM mailbox (leader CTA), by chunk parity
+    __shared__ dd sWarpTot[kBatchSlots][kThreads / 32];   // per-warp part totals, reduced once per batch
+    __shared__ dd sMine[kBatchSlots];                      // this CTA's part sums of the batch
+    __shared__ __align__(16) dd sMail[kBatchChunks];       // DSMEM mailbox (leader CTA)
     __shared__ dd sSeg[kSegments];
     __shared__ int sIsLast;
     constexpr bool kIsProfile = std::is_same<F, ProfileF>::value;
@@ -259,6 +256,7 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(DeviceState
     __shared__ __align__(8) uint64_t sBar;
 
     const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
     const uint32_t crank = ptx::cluster_ctarank();
     const uint32_t csize = ptx::cluster_nctarank();
 
@@ -266,16 +264,10 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(DeviceState
     uint64_t trace_t0 = 0, trace_tiles = 0;
     if (st.trace && tid == 0) trace_t0 = ptx::globaltimer();
 
-    // ---- plan (+ table) into shared memory ---------------------------------
-    {
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(st.plan);
-        uint32_t* dst = reinterpret_cast<uint32_t*>(&P);
-        for (int i = tid; i < int(sizeof(Plan) / 4); i += kThreads) dst[i] = __ldg(src + i);
-    }
-    if (kIsProfile && tid == 0) ptx::mbar_init(&sBar, 1);
-    __syncthreads();
     if (kIsProfile) {
         // One 1-D TMA bulk copy brings the whole table (14.4 KB by default).
+        if (tid == 0) ptx::mbar_init(&sBar, 1);
+        __syncthreads();
         const uint32_t bytes = ((P.table_len + 1u) & ~1u) * 8u;
         if (tid == 0) {
             ptx::mbar_expect_tx(&sBar, bytes);
@@ -285,59 +277,68 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(DeviceState
     }
 
     const F f = make_functor<F>(P, sTable);
-    const PartWorker<F, R, MODE> worker(P, f, sSC[tid >> 5], sX0[tid >> 5]);
+    const PartWorker<F, R, MODE> worker(P, f, sSC[warp], sX0[warp]);
 
     const uint32_t cluster_id = blockIdx.x / csize;
     const uint32_t n_clusters = gridDim.x / csize;
 
     // ---- chunks ------------------------------------------------------------
-    // Cluster pair: CTA q takes part q of the chunk; CTA 1 drops its part sum in
-    // CTA 0's DSMEM mailbox.  The cluster barrier is split: arrive right after
-    // the store, wait only one chunk later, so neither CTA idles while its
-    // partner finishes a part that is one tile longer.
-    uint32_t iter = 0;
-    bool pending = false;
-    dd pend_val{0.0, 0.0};
-    uint32_t pend_chunk = 0;
-    // A cluster owns a contiguous run of chunks: for small n the few chunks that
-    // hold a tile are evenly spaced, and a strided assignment would pile them
-    // all onto the same handful of clusters.
+    // A cluster owns a contiguous run of chunks (for small n the few chunks that
+    // hold a tile are evenly spaced; a strided assignment would pile them onto a
+    // handful of clusters).  With a cluster pair, CTA q takes part q of every
+    // chunk.  Nothing in the tile loop synchronises beyond a warp: every warp
+    // parks its total of a part in shared memory and moves on, and the
+    // CTA-wide / cluster-wide combine happens once per batch of kBatchChunks
+    // chunks — one __syncthreads and one cluster barrier per launch on the
+    // default grid, instead of one of each per chunk.
     const uint32_t per_cluster = (P.chunk_hi - P.chunk_lo + n_clusters - 1) / n_clusters;
     const uint32_t my_lo = P.chunk_lo + cluster_id * per_cluster;
     const uint32_t my_hi = my_lo + per_cluster < P.chunk_hi ? my_lo + per_cluster : P.chunk_hi;
-    for (uint32_t chunk = my_lo; chunk < my_hi; ++chunk) {
-        {   // Small n leaves most chunks without a tile: no reduction, no barrier for those.
-            uint64_t lo0, hi0, lo1, hi1;
-            part_tiles(P, chunk * kPartsPerChunk, lo0, hi0);
-            part_tiles(P, chunk * kPartsPerChunk + 1, lo1, hi1);
-            if (st.trace) trace_tiles += (csize == 2) ? (crank ? hi1 - lo1 : hi0 - lo0) : hi1 - lo0;
-            if (lo0 >= hi1) {
-                if (crank == 0 && tid == 0) st.partials[chunk] = dd{0.0, 0.0};
-                continue;
+    const uint32_t pp = (csize == 2) ? 1u : uint32_t(kPartsPerChunk);   // parts per chunk done here
+    for (uint32_t b_lo = my_lo; b_lo < my_hi; b_lo += kBatchChunks) {
+        const uint32_t nb = my_hi - b_lo < uint32_t(kBatchChunks) ? my_hi - b_lo : uint32_t(kBatchChunks);
+        for (uint32_t k = 0; k < nb; ++k) {
+            for (uint32_t q = 0; q < pp; ++q) {
+                const uint32_t part = (b_lo + k) * kPartsPerChunk + (csize == 2 ? crank : q);
+                if (st.trace) {
+                    uint64_t lo, hi;
+                    part_tiles(P, part, lo, hi);
+                    trace_tiles += hi - lo;
+                }
+                const dd t = warp_reduce_lazy(worker.run(part));
+                if (lane == 0) sWarpTot[k * pp + q][warp] = t;
             }
         }
-        if (csize == 2) {
-            const dd mine = block_reduce_dd(worker.run(chunk * kPartsPerChunk + crank), swarp);
-            if (pending) {
-                ptx::cluster_wait();
-                if (crank == 0 && tid == 0) st.partials[pend_chunk] = dd_add(pend_val, sPeer[(iter - 1) & 1]);
+        __syncthreads();
+        // Part sums: warp w finishes slots w, w + 8 (the 8-lane butterfly + one
+        // renormalisation).
+        for (uint32_t s = warp; s < nb * pp; s += kThreads / 32) {
+            dd r = lane < kThreads / 32 ? sWarpTot[s][lane] : dd{0.0, 0.0};
+#pragma unroll
+            for (int off = 4; off >= 1; off >>= 1) r = dd_add_lazy(r, shfl_xor_dd(r, off));
+            r = dd_renorm(r);
+            if (lane == 0) {
+                if (csize == 2 && crank == 1)
+                    ptx::st_dsmem_f64x2(ptx::mapa(&sMail[s], 0), r.hi, r.lo);   // partner's mailbox
+                else
+                    sMine[s] = r;
             }
-            if (crank == 1 && tid == 0)
-                ptx::st_dsmem_f64x2(ptx::mapa(&sPeer[iter & 1], 0), mine.hi, mine.lo);
-            ptx::cluster_arrive();
-            pending = true;
-            pend_val = mine;
-            pend_chunk = chunk;
-            ++iter;
-        } else {
-            const dd p0 = block_reduce_dd(worker.run(chunk * kPartsPerChunk + 0), swarp);
-            const dd p1 = block_reduce_dd(worker.run(chunk * kPartsPerChunk + 1), swarp);
-            if (tid == 0) st.partials[chunk] = dd_add(p0, p1);
         }
-    }
-    if (pending) {
-        ptx::cluster_wait();
-        if (crank == 0 && tid == 0) st.partials[pend_chunk] = dd_add(pend_val, sPeer[(iter - 1) & 1]);
+        if (csize == 2)
+            ptx::cluster_sync_all();    // mailbox complete (release/acquire), also a CTA barrier
+        else
+            __syncthreads();
+        if (crank == 0 && uint32_t(tid) < nb) {
+            const dd p0 = sMine[tid * pp];
+            const dd p1 = (csize == 2) ? sMail[tid] : sMine[tid * pp + 1];
+            st.partials[b_lo + tid] = dd_add(p0, p1);
+        }
+        if (b_lo + kBatchChunks < my_hi) {   // another batch reuses the slots and the mailbox
+            if (csize == 2)
+                ptx::cluster_sync_all();
+            else
+                __syncthreads();
+        }
     }
     if (st.trace && tid == 0) {
         uint32_t smid;
@@ -348,6 +349,7 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(DeviceState
     if (crank != 0) return;
 
     // ---- ticket: who is last? ------------------------------------------------
+    __syncthreads();                 // every chunk sum of this cluster is stored
     if (tid == 0) {
         __threadfence();
         const unsigned int t = atomicAdd(st.ticket, 1u);
@@ -358,19 +360,26 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(DeviceState
     __threadfence();
 
     // ---- segment sums: one warp per owned segment, fixed order ---------------
-    const int warp = tid >> 5, lane = tid & 31;
     if (tid < kSegments) sSeg[tid] = dd{0.0, 0.0};
     __syncthreads();
     {
         const uint32_t seg = P.seg_lo + warp;
         if (seg < P.seg_hi) {
-            dd acc{0.0, 0.0};
+            constexpr int kPerLane = (kChunksPerSegment + 31) / 32;
             const uint32_t c0 = seg * kChunksPerSegment;
-            for (uint32_t c = c0 + lane; c < c0 + kChunksPerSegment; c += 32) {
-                double hi, lo;
-                ptx::ld_relaxed_sys_f64x2(reinterpret_cast<const double*>(st.partials + c), hi, lo);
-                acc = dd_add(acc, dd{hi, lo});
+            // all loads in flight first, then the same in-order fold as ever
+            double hi[kPerLane], lo[kPerLane];
+#pragma unroll
+            for (int i = 0; i < kPerLane; ++i) {
+                const uint32_t c = c0 + lane + 32 * i;
+                hi[i] = lo[i] = 0.0;
+                if (c < c0 + kChunksPerSegment)
+                    ptx::ld_relaxed_sys_f64x2(reinterpret_cast<const double*>(st.partials + c), hi[i], lo[i]);
             }
+            dd acc{0.0, 0.0};
+#pragma unroll
+            for (int i = 0; i < kPerLane; ++i)
+                if (c0 + lane + 32 * i < c0 + kChunksPerSegment) acc = dd_add(acc, dd{hi[i], lo[i]});
             acc = warp_reduce_dd(acc);
             if (lane == 0) sSeg[seg] = acc;
         }
@@ -424,12 +433,25 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(DeviceState
         *st.ticket = 0u;
         st.result->t_end_ns = ptx::globaltimer();
     }
+    // The device -> host leg of the call: the result block goes straight into
+    // the context's pinned, mapped host block (one 8-byte word per lane, a
+    // single PCIe write burst) — no copy engine operation follows the kernel.
+    if (st.result_host) {
+        __syncwarp();
+        static_assert(sizeof(bq_result) % 8 == 0 && sizeof(bq_result) / 8 <= 32, "result block = one word per lane");
+        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(st.result);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(st.result_host);
+        if (lane < int(sizeof(bq_result) / 8)) dst[lane] = src[lane];
+    }
 }
 
 // ---- dispatch ----------------------------------------------------------------
 
 template <class F, class R, int MODE>
-static cudaError_t launch_one(const DeviceState& st, const LaunchConfig& cfg, cudaStream_t stream) {
+static cudaError_t launch_one(const Plan& P, const DeviceState& st, const LaunchConfig& cfg, cudaStream_t stream) {
+    QuadParams prm;
+    prm.P = P;
+    prm.st = st;
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(cfg.grid, 1, 1);
     lc.blockDim = dim3(kThreads, 1, 1);
@@ -442,7 +464,7 @@ static cudaError_t launch_one(const DeviceState& st, const LaunchConfig& cfg, cu
     attr[0].val.clusterDim.z = 1;
     lc.attrs = attr;
     lc.numAttrs = 1;
-    return cudaLaunchKernelEx(&lc, quad_kernel<F, R, MODE>, st);
+    return cudaLaunchKernelEx(&lc, quad_kernel<F, R, MODE>, prm);
 }
 
 template <class F>
@@ -451,13 +473,13 @@ static cudaError_t launch_f(const Plan& P, const DeviceState& st, const LaunchCo
     const bool rot = P.eval == BQ_EVAL_ROTATE;
     if constexpr (F::kTrig) {
         if (P.dtype == BQ_F64)
-            return rot ? launch_one<F, double, BQ_EVAL_ROTATE>(st, cfg, stream)
-                       : launch_one<F, double, BQ_EVAL_DIRECT>(st, cfg, stream);
-        return rot ? launch_one<F, float, BQ_EVAL_ROTATE>(st, cfg, stream)
-                   : launch_one<F, float, BQ_EVAL_DIRECT>(st, cfg, stream);
+            return rot ? launch_one<F, double, BQ_EVAL_ROTATE>(P, st, cfg, stream)
+                       : launch_one<F, double, BQ_EVAL_DIRECT>(P, st, cfg, stream);
+        return rot ? launch_one<F, float, BQ_EVAL_ROTATE>(P, st, cfg, stream)
+                   : launch_one<F, float, BQ_EVAL_DIRECT>(P, st, cfg, stream);
     } else {
-        if (P.dtype == BQ_F64) return launch_one<F, double, BQ_EVAL_DIRECT>(st, cfg, stream);
-        return launch_one<F, float, BQ_EVAL_DIRECT>(st, cfg, stream);
+        if (P.dtype == BQ_F64) return launch_one<F, double, BQ_EVAL_DIRECT>(P, st, cfg, stream);
+        return launch_one<F, float, BQ_EVAL_DIRECT>(P, st, cfg, stream);
     }
 }
 
