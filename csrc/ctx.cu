@@ -235,11 +235,8 @@ static LaunchConfig quad_config(const bq_ctx* c, const Plan& P) {
     LaunchConfig cfg;
     cfg.cluster = unsigned(c->cluster);
     unsigned grid = unsigned(c->sm_count * c->ctas_per_sm);
-    // Small n: this rank holds only a few tiles, so launch only as many CTAs as
-    // get one each (the grid shape never changes the result, see plan.h).
-    const uint64_t my_tiles = (P.n_tiles + uint64_t(P.world) - 1) / uint64_t(P.world);
-    if (my_tiles < grid) grid = unsigned(my_tiles ? my_tiles : 1);
-    grid += (cfg.cluster - grid % cfg.cluster) % cfg.cluster;
+    (void)P;   // the grid is the same for every n: a cluster never owns more than a few chunks
+    grid -= grid % cfg.cluster;
     if (grid < cfg.cluster) grid = cfg.cluster;
     cfg.grid = grid;
     return cfg;

@@ -23,6 +23,11 @@ __device__ __forceinline__ uint64_t ld_acquire_gpu(const uint64_t* p) {
     asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void st_release_gpu(uint64_t* p, uint64_t v) {
     asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
@@ -51,6 +56,9 @@ __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" 
 __device__ __forceinline__ void st_f64x4(double* p, double a, double b, double c, double d) {
     asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d)
                  : "memory");
+}
+__device__ __forceinline__ void st_f64x2(double* p, double a, double b) {
+    asm volatile("st.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(a), "d"(b) : "memory");
 }
 // Streaming variant for outputs that are written once and read by another kernel.
 __device__ __forceinline__ void st_cs_f64x2(double* p, double a, double b) {

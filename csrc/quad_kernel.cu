@@ -63,10 +63,10 @@ template <class F, class R, int MODE>
 struct PartWorker {
     static constexpr bool kRotate = (MODE == BQ_EVAL_ROTATE);
 
-    const Plan& P;        // shared-memory copy (per-tile geometry only)
+    const Plan& P;        // kernel parameter (constant bank)
     const F& f;
-    Vec2<R>* wSC;         // this warp's private row bases: [2][kMaxRows]
-    double* wX0;          // this warp's private row x0:    [2][kMaxRows]
+    Vec2<R>* wSC;         // this warp's private row bases: [2][kBufStride]
+    double* wX0;          // this warp's private row x0:    [2][kBufStride] (integrands that need x)
     const double h, a;    // register copies for the hot loops
     const uint32_t rows;  // rows of every tile but the last
     const uint64_t last_tile, tile_pts;
@@ -118,19 +118,79 @@ struct PartWorker {
         return g;
     }
 
-    // Row bases of one tile: lane r rotates the tile base by r rows (4 fp64 ops)
-    // and parks the pair in this warp's private shared-memory slot.
-    __device__ __forceinline__ void row_bases(uint64_t tile, SinCos tb, int buf) const {
+    // Rows of a flush group: kFlushTiles tiles x kMaxRows rows.  The row bases of a
+    // whole group sit contiguously in this warp's buffer, so a group of full
+    // tiles is one software-pipelined loop of kGroupRows rows.
+    static constexpr int kGroupRows = kFlushTiles * kMaxRows;
+    static constexpr int kBufStride = kGroupRows + 2;   // +1 prefetch slot, kept even
+
+    // Row bases of the group of `nt` tiles starting at tile t0: for each tile,
+    // lane r rotates the tile base by r rows (4 fp64 ops) and parks the pair in
+    // this warp's private buffer.  `grp` carries the accurate tile bases of the
+    // current run of 32 tiles (refreshed here when t0 starts a new run).
+    __device__ __forceinline__ void group_row_bases(uint32_t t0, uint32_t nt, uint32_t lo, uint32_t hi,
+                                                    SinCos& grp, int buf) const {
         const int lane = threadIdx.x & 31;
-        const SinCos rb = rotate_sc(tb, rowrot);
-        wSC[buf * kMaxRows + lane] = Vec2<R>{R(rb.s), R(rb.c)};
-        if (F::kNeedX)
-            wX0[buf * kMaxRows + lane] =
-                fma(double(tile * tile_pts + uint64_t(lane) * kWidth) + P.off, h, a);
+        if (((t0 - lo) & 31u) == 0u) grp = group_bases(t0, hi);
+        Vec2<R>* sc = wSC + buf * kBufStride + lane;
+        double* x0 = wX0 + buf * kBufStride + lane;
+#pragma unroll
+        for (uint32_t k = 0; k < uint32_t(kFlushTiles); ++k) {
+            if (k < nt) {
+                const int src = int((t0 + k - lo) & 31u);
+                const SinCos tb{__shfl_sync(0xffffffffu, grp.s, src), __shfl_sync(0xffffffffu, grp.c, src)};
+                const SinCos rb = rotate_sc(tb, rowrot);
+                sc[k * kMaxRows] = Vec2<R>{R(rb.s), R(rb.c)};
+                if (F::kNeedX)
+                    x0[k * kMaxRows] =
+                        fma(double(uint64_t(t0 + k) * tile_pts + uint64_t(lane) * kWidth) + P.off, h, a);
+            }
+        }
     }
 
-    // Adds every sample of `tile` into `acc`.  Only the globally last tile can be short.
-    __device__ __forceinline__ void tile_accumulate(uint64_t tile, int buf, TileAcc<R>& acc) const {
+    // `nrows` full rows starting at row-base slot 0 of sc_row / x0_row.
+    // Software-pipelined: the next row's base is in flight while this row's
+    // 24 fp64 instructions issue (slot nrows is valid memory).
+    template <class Count>
+    __device__ __forceinline__ void rows_rotate(const Vec2<R>* sc_row, const double* x0_row, Count nrows,
+                                                TileAcc<R>& acc, Vec2<R>& sc, double& x0) const {
+        sc = sc_row[0];
+        x0 = F::kNeedX ? x0_row[0] : 0.0;
+#pragma unroll 4
+        for (Count r = 0; r < nrows; ++r) {
+            const Vec2<R> sc_next = sc_row[r + 1];
+            const double x0_next = F::kNeedX ? x0_row[r + 1] : 0.0;
+            R v[kCols];
+#pragma unroll
+            for (int j = 0; j < kCols; ++j)
+                v[j] = point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]);
+            acc.add_row(v);
+            sc = sc_next;
+            x0 = x0_next;
+        }
+    }
+
+    // ROTATE, any tile (short last tile, tiles of fewer than kMaxRows rows).
+    __device__ __forceinline__ void tile_rotate(uint32_t tile, const Vec2<R>* sc_row, const double* x0_row,
+                                                TileAcc<R>& acc) const {
+        uint32_t full_rows = rows, rem = 0;
+        if (tile == last_tile) {
+            const TileGeom g = tile_geom(P, tile);
+            full_rows = g.full_rows, rem = g.rem;
+        }
+        Vec2<R> sc;
+        double x0;
+        rows_rotate<uint32_t>(sc_row, x0_row, full_rows, acc, sc, x0);
+        if (rem) {   // sc / x0 already hold row full_rows
+#pragma unroll
+            for (int j = 0; j < kCols; ++j)
+                if (threadIdx.x + kThreads * j < rem)
+                    acc.add_one(j, point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]));
+        }
+    }
+
+    // DIRECT: adds every sample of `tile` into `acc`.  Only the globally last tile can be short.
+    __device__ __forceinline__ void tile_direct(uint64_t tile, TileAcc<R>& acc) const {
         TileGeom g;
         if (tile == last_tile) {
             g = tile_geom(P, tile);
@@ -139,88 +199,68 @@ struct PartWorker {
             g.full_rows = rows;
             g.rem = 0;
         }
-        if (kRotate) {
-            const Vec2<R>* sc_row = wSC + buf * kMaxRows;
-            const double* x0_row = wX0 + buf * kMaxRows;
-            // Software-pipelined: the next row's base is in flight while this row's
-            // 24 fp64 instructions issue (index full_rows is a valid slot).
-            Vec2<R> sc = sc_row[0];
-            double x0 = F::kNeedX ? x0_row[0] : 0.0;
-#pragma unroll 4
-            for (uint32_t r = 0; r < g.full_rows; ++r) {
-                const Vec2<R> sc_next = sc_row[r + 1];
-                const double x0_next = F::kNeedX ? x0_row[r + 1] : 0.0;
-                R v[kCols];
-#pragma unroll
-                for (int j = 0; j < kCols; ++j)
-                    v[j] = point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]);
-                acc.add_row(v);
-                sc = sc_next;
-                x0 = x0_next;
-            }
-            if (g.rem) {   // sc / x0 already hold row full_rows
-#pragma unroll
-                for (int j = 0; j < kCols; ++j)
-                    if (threadIdx.x + kThreads * j < g.rem)
-                        acc.add_one(j, point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]));
-            }
-        } else {
-            double rb = row_base_index(P, g, 0);
+        double rb = row_base_index(P, g, 0);
 #pragma unroll 2
-            for (uint32_t r = 0; r < g.full_rows; ++r) {
-                R v[kCols];
+        for (uint32_t r = 0; r < g.full_rows; ++r) {
+            R v[kCols];
 #pragma unroll
-                for (int j = 0; j < kCols; ++j) v[j] = point_direct<F, R>(f, rb, dx[j], h, a);
-                acc.add_row(v);
-                rb += double(kWidth);
-            }
-            if (g.rem) {
+            for (int j = 0; j < kCols; ++j) v[j] = point_direct<F, R>(f, rb, dx[j], h, a);
+            acc.add_row(v);
+            rb += double(kWidth);
+        }
+        if (g.rem) {
 #pragma unroll
-                for (int j = 0; j < kCols; ++j)
-                    if (threadIdx.x + kThreads * j < g.rem)
-                        acc.add_one(j, point_direct<F, R>(f, rb, dx[j], h, a));
-            }
+            for (int j = 0; j < kCols; ++j)
+                if (threadIdx.x + kThreads * j < g.rem)
+                    acc.add_one(j, point_direct<F, R>(f, rb, dx[j], h, a));
         }
     }
 
     // All tiles of one part; returns this thread's dd total.  In ROTATE mode a
-    // warp is self-sufficient (its own bases, its own shared-memory slot), so
-    // the tile loop has no CTA-wide barrier.
+    // warp is self-sufficient (its own bases, its own shared-memory buffer), so
+    // the tile loop has no CTA-wide barrier, and a flush group of full tiles
+    // runs as one loop: one warp-level sync and one compensated flush per
+    // kFlushTiles tiles.
     __device__ __forceinline__ dd run(uint32_t part) const {
-        uint64_t lo, hi;
-        part_tiles(P, part, lo, hi);
+        uint64_t lo64, hi64;
+        part_tiles(P, part, lo64, hi64);
         dd total{0.0, 0.0};
         TileAcc<R> acc;
         acc.clear();
         if (kRotate) {
+            const uint32_t lo = uint32_t(lo64), hi = uint32_t(hi64);   // n_tiles < 2^31
             if (lo >= hi) return total;
-            uint64_t gfirst = lo;
-            SinCos grp = group_bases(gfirst, hi);
-            row_bases(lo, SinCos{__shfl_sync(0xffffffffu, grp.s, 0), __shfl_sync(0xffffffffu, grp.c, 0)}, 0);
-            __syncwarp();
+            const uint32_t last = uint32_t(last_tile);
+            SinCos grp{0.0, 1.0};
             int buf = 0;
-            for (uint64_t t = lo; t < hi; ++t) {
-                if (t + 1 < hi) {
-                    if (t + 1 - gfirst == 32) {
-                        gfirst = t + 1;
-                        grp = group_bases(gfirst, hi);
-                    }
-                    const int src = int(t + 1 - gfirst);
-                    row_bases(t + 1, SinCos{__shfl_sync(0xffffffffu, grp.s, src),
-                                            __shfl_sync(0xffffffffu, grp.c, src)}, buf ^ 1);
+            group_row_bases(lo, hi - lo < uint32_t(kFlushTiles) ? hi - lo : uint32_t(kFlushTiles), lo, hi, grp, 0);
+            __syncwarp();
+            for (uint32_t t = lo; t < hi; t += kFlushTiles) {
+                const uint32_t nt = hi - t < uint32_t(kFlushTiles) ? hi - t : uint32_t(kFlushTiles);
+                if (t + kFlushTiles < hi) {
+                    const uint32_t left = hi - t - kFlushTiles;
+                    group_row_bases(t + kFlushTiles, left < uint32_t(kFlushTiles) ? left : uint32_t(kFlushTiles),
+                                    lo, hi, grp, buf ^ 1);
                 }
-                tile_accumulate(t, buf, acc);
-                if (((t - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || t + 1 == hi) {
-                    total = dd_acc_lazy(total, acc.flush());
-                    acc.clear();
+                const Vec2<R>* sc_row = wSC + buf * kBufStride;
+                const double* x0_row = wX0 + buf * kBufStride;
+                if (nt == uint32_t(kFlushTiles) && rows == uint32_t(kMaxRows) && t + kFlushTiles - 1 < last) {
+                    Vec2<R> sc;
+                    double x0;
+                    rows_rotate<int>(sc_row, x0_row, kGroupRows, acc, sc, x0);
+                } else {
+                    for (uint32_t k = 0; k < nt; ++k)
+                        tile_rotate(t + k, sc_row + k * kMaxRows, x0_row + k * kMaxRows, acc);
                 }
+                total = dd_acc_lazy(total, acc.flush());
+                acc.clear();
                 __syncwarp();
                 buf ^= 1;
             }
         } else {
-            for (uint64_t t = lo; t < hi; ++t) {
-                tile_accumulate(t, 0, acc);
-                if (((t - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || t + 1 == hi) {
+            for (uint64_t t = lo64; t < hi64; ++t) {
+                tile_direct(t, acc);
+                if (((t - lo64) & (kFlushTiles - 1)) == kFlushTiles - 1 || t + 1 == hi64) {
                     total = dd_acc_lazy(total, acc.flush());
                     acc.clear();
                 }
@@ -244,8 +284,11 @@ template <class F, class R, int MODE>
 __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __grid_constant__ QuadParams prm) {
     const Plan& P = prm.P;
     const DeviceState& st = prm.st;
-    __shared__ Vec2<R> sSC[kThreads / 32][2 * kMaxRows + 2];   // warp-private row bases (+pad)
-    __shared__ double sX0[kThreads / 32][2 * kMaxRows + 2];
+    // warp-private row-base buffers (ROTATE only), sized by rotate_smem_bytes()
+    extern __shared__ __align__(16) unsigned char sDyn[];
+    using Worker = PartWorker<F, R, MODE>;
+    Vec2<R>* const sSC = reinterpret_cast<Vec2<R>*>(sDyn);
+    double* const sX0 = reinterpret_cast<double*>(sDyn + sizeof(Vec2<R>) * (kThreads / 32) * 2 * Worker::kBufStride);
     __shared__ dd sWarpTot[kBatchSlots][kThreads / 32];   // per-warp part totals, reduced once per batch
     __shared__ dd sMine[kBatchSlots];                      // this CTA's part sums of the batch
     __shared__ __align__(16) dd sMail[kBatchChunks];       // DSMEM mailbox (leader CTA)
@@ -277,7 +320,8 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     }
 
     const F f = make_functor<F>(P, sTable);
-    const PartWorker<F, R, MODE> worker(P, f, sSC[warp], sX0[warp]);
+    const Worker worker(P, f, sSC + warp * 2 * Worker::kBufStride,
+                        sX0 + (F::kNeedX ? warp * 2 * Worker::kBufStride : 0));
 
     const uint32_t cluster_id = blockIdx.x / csize;
     const uint32_t n_clusters = gridDim.x / csize;
@@ -300,12 +344,11 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
         for (uint32_t k = 0; k < nb; ++k) {
             for (uint32_t q = 0; q < pp; ++q) {
                 const uint32_t part = (b_lo + k) * kPartsPerChunk + (csize == 2 ? crank : q);
-                if (st.trace) {
-                    uint64_t lo, hi;
-                    part_tiles(P, part, lo, hi);
-                    trace_tiles += hi - lo;
-                }
-                const dd t = warp_reduce_lazy(worker.run(part));
+                uint64_t lo, hi;
+                part_tiles(P, part, lo, hi);
+                trace_tiles += hi - lo;
+                dd t{0.0, 0.0};
+                if (lo < hi) t = warp_reduce_lazy(worker.run(part));   // small n: most parts hold no tile
                 if (lane == 0) sWarpTot[k * pp + q][warp] = t;
             }
         }
@@ -447,6 +490,15 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
 
 // ---- dispatch ----------------------------------------------------------------
 
+// Dynamic shared memory of one CTA: the warp-private row-base buffers of ROTATE.
+template <class F, class R, int MODE>
+constexpr size_t rotate_smem_bytes() {
+    using W = PartWorker<F, R, MODE>;
+    return MODE == BQ_EVAL_ROTATE
+               ? size_t(kThreads / 32) * 2 * W::kBufStride * (sizeof(Vec2<R>) + (F::kNeedX ? sizeof(double) : 0))
+               : 0;
+}
+
 template <class F, class R, int MODE>
 static cudaError_t launch_one(const Plan& P, const DeviceState& st, const LaunchConfig& cfg, cudaStream_t stream) {
     QuadParams prm;
@@ -455,8 +507,22 @@ static cudaError_t launch_one(const Plan& P, const DeviceState& st, const Launch
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(cfg.grid, 1, 1);
     lc.blockDim = dim3(kThreads, 1, 1);
-    lc.dynamicSmemBytes = 0;
+    lc.dynamicSmemBytes = rotate_smem_bytes<F, R, MODE>();
     lc.stream = stream;
+    if (lc.dynamicSmemBytes > 48 * 1024) {
+        // above the default limit (only the double-precision x-dependent trig integrand): opt in,
+        // once per device
+        static bool done[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !done[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(quad_kernel<F, R, MODE>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 int(lc.dynamicSmemBytes));
+            if (e != cudaSuccess) return e;
+            done[dev] = true;
+        }
+    }
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cfg.cluster;

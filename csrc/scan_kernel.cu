@@ -4,19 +4,26 @@
 // sum, gather to root, serial carry fix-up on the root, MPI_Bcast of 144 MB —
 // twice.  Here, per GPU, in a single persistent launch:
 //
-//   phase A   every CTA reduces its tiles to (sum v, sum of local running sums);
-//             f is evaluated on the fly, no sample array is ever materialised
-//   phase A'  the last CTA to finish turns the tile aggregates of each owned
-//             segment into exclusive prefixes (fixed-shape block scan, dd),
+//   phase A   every WARP reduces whole tiles to (sum v, sum of local running
+//             sums); f is evaluated on the fly, no sample array is ever
+//             materialised, and no CTA-wide barrier sits in the tile loop
+//   phase A'  once every tile aggregate is in, one CTA per owned segment turns
+//             that segment's aggregates into exclusive prefixes (fixed-shape
+//             block scan, dd) — the segments in parallel; the last of them
 //             publishes the segment totals into every peer's comm block over
 //             NVLink, meets the peers at an in-kernel barrier and folds the 8
 //             totals in order into segment bases        (replaces 4main.c:134-155)
-//   phase B   every CTA re-evaluates its tiles, scans them with the right base
-//             and streams P and Q out — into every peer's table as well when
-//             replicate is on (the fused all-gather that replaces MPI_Bcast,
-//             4main.c:157,221)
+//   phase B   every warp re-evaluates its tiles, scans them with the right base
+//             and streams P and Q out in 256-bit stores — into every peer's
+//             table as well when replicate is on (the fused all-gather that
+//             replaces MPI_Bcast, 4main.c:157,221)
 //   end       second in-kernel barrier: when the kernel retires, every rank's
 //             stores into this GPU's tables and the three final scalars are visible
+//
+// A tile is 2048 samples = 8 passes of 32 lanes x 8 samples.  The arithmetic
+// tree of a tile (scan_core.cuh) is that of a 256-thread block scan; one warp
+// walks it pass by pass, so the result does not depend on which warp or CTA
+// ran the tile, and matches cpu_scan.cpp bit for bit.
 //
 // CTAs of one launch wait on each other, so the grid never exceeds what is
 // co-resident (cooperative launch attribute).
@@ -36,12 +43,8 @@ namespace {
 constexpr int kWarps = kScanThreads / 32;
 
 struct ScanSmem {
-    ScanPlan P;
-    double red[2][kWarps];
     Run warp_tot[kWarps];
-    Run2 warp_tot2[kWarps];
     Run seg_tot[kSegments];
-    Run2 tile_excl;
     uint64_t gen;
     int is_last;
     int status;
@@ -113,8 +116,20 @@ __device__ void segment_prefixes(const ScanPlan& P, const ScanState& st, int seg
     __syncthreads();
 }
 
+struct ScanParams {
+    ScanPlan P;        // rides in the kernel parameter buffer
+    ScanState st;
+};
+
+// (a0 .. a7) summed in the order of an 8-lane xor butterfly (offsets 4, 2, 1).
+__device__ __forceinline__ double butterfly8(const double (&a)[8]) {
+    return ((a[0] + a[4]) + (a[2] + a[6])) + ((a[1] + a[5]) + (a[3] + a[7]));
+}
+
 template <class F>
-__global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanState st) {
+__global__ void __launch_bounds__(kScanThreads, 4) scan_kernel(const __grid_constant__ ScanParams prm) {
+    const ScanPlan& P = prm.P;
+    const ScanState& st = prm.st;
     __shared__ ScanSmem sm;
     constexpr bool kIsProfile = std::is_same<F, ProfileF>::value;
     __shared__ __align__(16) double sTable[kIsProfile ? kMaxTable : 2];
@@ -122,18 +137,12 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanState st) {
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (blockIdx.x == 0 && tid == 0) st.result->t_start_ns = ptx::globaltimer();
-    {
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(st.plan);
-        uint32_t* dst = reinterpret_cast<uint32_t*>(&sm.P);
-        for (int i = tid; i < int(sizeof(ScanPlan) / 4); i += kScanThreads) dst[i] = __ldg(src + i);
-    }
     if (tid == 0) {
         sm.gen = ptx::ld_acquire_gpu(st.ready + 1) + 1;   // generation of this launch
         sm.status = BQ_OK;
         if (kIsProfile) ptx::mbar_init(&sBar, 1);
     }
     __syncthreads();
-    const ScanPlan& P = sm.P;
     if (kIsProfile) {
         const uint32_t bytes = ((P.table_len + 1u) & ~1u) * 8u;
         if (tid == 0) {
@@ -149,48 +158,78 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanState st) {
     const uint64_t limit = uint64_t(P.timeout_ms) * 1000000ull;
     const uint64_t gen = sm.gen;
     const bool multi = P.world > 1;
+    const uint64_t gwarp = uint64_t(blockIdx.x) * kWarps + warp;
+    const uint64_t nwarps = uint64_t(gridDim.x) * kWarps;
 
-    // ---- phase A: tile aggregates -------------------------------------------
-    for (uint64_t tile = P.tile_lo + blockIdx.x; tile < P.tile_hi; tile += gridDim.x) {
+    // ---- phase A: tile aggregates, one warp per tile ---------------------------
+    for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
         const uint32_t m = scan_tile_count(P, tile);
-        const uint32_t k0 = uint32_t(tid) * kScanItems;
-        double v[kScanItems];
-        scan_thread_values(f, P, tile * uint64_t(kScanTile) + k0, k0, m, v);
-        double s, w;
-        scan_thread_aggregate(v, k0, m, s, w);
-        s = warp_sum(s);
-        w = warp_sum(w);
-        if (lane == 0) sm.red[0][warp] = s, sm.red[1][warp] = w;
-        __syncthreads();
-        if (warp == 0) {
-            double a = lane < kWarps ? sm.red[0][lane] : 0.0;
-            double b = lane < kWarps ? sm.red[1][lane] : 0.0;
+        double a[kWarps], b[kWarps];
 #pragma unroll
-            for (int off = 4; off >= 1; off >>= 1) {
-                a += __shfl_xor_sync(0xffffffffu, a, off);
-                b += __shfl_xor_sync(0xffffffffu, b, off);
+        for (int j = 0; j < kWarps; ++j) {   // pass j = the samples of "warp j" of a block scan
+            const uint32_t k0 = uint32_t(j * 32 + lane) * kScanItems;
+            double v[kScanItems];
+            scan_thread_values(f, P, tile * uint64_t(kScanTile) + k0, k0, m, v);
+            double s, w;
+            scan_thread_aggregate(v, k0, m, s, w);
+            a[j] = warp_sum(s);
+            b[j] = warp_sum(w);
+        }
+        if (lane == 0) ptx::st_f64x2(st.agg + 2 * (tile - P.tile_lo), butterfly8(a), butterfly8(b));
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        atomicAdd(st.ticket_a, 1u);
+    }
+
+    // ---- phase A': prefixes (segments in parallel), exchange, segment bases -----
+    const uint32_t owned = P.seg_hi - P.seg_lo;
+    const uint32_t workers = owned < gridDim.x ? owned : gridDim.x;
+    if (blockIdx.x < workers) {
+        if (tid == 0) {
+            const uint64_t t0 = ptx::globaltimer();
+            while (ptx::ld_acquire_gpu_u32(st.ticket_a) < gridDim.x) {
+                if (ptx::globaltimer() - t0 > 4 * limit) {
+                    sm.status = BQ_ERR_TIMEOUT;
+                    break;
+                }
             }
-            if (lane == 0) {
-                double* o = st.agg + 2 * (tile - P.tile_lo);
-                o[0] = a, o[1] = b;
+        }
+        if (tid < kSegments) sm.seg_tot[tid] = run_identity();
+        __syncthreads();
+        __threadfence();
+        for (uint32_t s = P.seg_lo + blockIdx.x; s < P.seg_hi; s += workers) {
+            segment_prefixes(P, st, int(s), sm);
+            if (tid == 0) {
+                // This segment's total goes where a peer would publish it: the slot of
+                // this call's parity in the own comm block, for the CTA that folds the bases.
+                const Run r = sm.seg_tot[s];
+                double* o = &st.comm->scan_slots[int(st.comm->scan_epoch & 1)][s][0];
+                ptx::st_relaxed_sys_f64x2(o, r.p.hi, r.p.lo);
+                ptx::st_relaxed_sys_f64x2(o + 2, r.q.hi, r.q.lo);
             }
         }
         __syncthreads();
-    }
-    if (tid == 0) {
-        __threadfence();
-        sm.is_last = (atomicAdd(st.ticket_a, 1u) == gridDim.x - 1);
-    }
-    __syncthreads();
-
-    // ---- phase A': prefixes, cross-GPU exchange, segment bases -----------------
-    if (sm.is_last) {
-        __threadfence();
-        if (tid < kSegments) sm.seg_tot[tid] = run_identity();
+        if (tid == 0) {
+            __threadfence();
+            sm.is_last = (atomicAdd(st.ticket_a + 1, 1u) == workers - 1);
+        }
         __syncthreads();
-        for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s) segment_prefixes(P, st, int(s), sm);
-        if (warp == 0) {
-            int status = BQ_OK;
+        if (sm.is_last && warp == 0) {
+            __threadfence();
+            int status = sm.status;
+            if (lane == 0) st.result->reserved[0] = ptx::globaltimer();   // all prefixes done
+            if (lane < kSegments) {
+                Run r = run_identity();
+                if (uint32_t(lane) >= P.seg_lo && uint32_t(lane) < P.seg_hi) {
+                    const double* o = &st.comm->scan_slots[int(st.comm->scan_epoch & 1)][lane][0];
+                    ptx::ld_relaxed_sys_f64x2(o, r.p.hi, r.p.lo);
+                    ptx::ld_relaxed_sys_f64x2(o + 2, r.q.hi, r.q.lo);
+                }
+                sm.seg_tot[lane] = r;
+            }
+            __syncwarp();
             if (multi) {
                 const uint64_t epoch = st.comm->scan_epoch;
                 const int par = int(epoch & 1);
@@ -212,6 +251,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanState st) {
                     Run r;
                     ptx::ld_relaxed_sys_f64x2(&st.comm->scan_slots[par][lane][0], r.p.hi, r.p.lo);
                     ptx::ld_relaxed_sys_f64x2(&st.comm->scan_slots[par][lane][2], r.q.hi, r.q.lo);
+                    r.cnt = 0.0;
                     sm.seg_tot[lane] = r;
                 }
                 __syncwarp();
@@ -229,7 +269,9 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanState st) {
                     base = run_combine(base, t);
                 }
                 st.result->status = status;
-                *st.ticket_a = 0u;
+                st.ticket_a[0] = 0u;
+                st.ticket_a[1] = 0u;
+                st.result->reserved[1] = ptx::globaltimer();                // bases ready
                 __threadfence();
                 ptx::st_release_gpu(st.ready, gen);
             }
@@ -240,93 +282,107 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanState st) {
     }
     __syncthreads();
 
-    // ---- phase B: scan + store ------------------------------------------------
+    // ---- phase B: scan + store, one warp per tile --------------------------------
     const bool replicate = multi && (P.flags & kScanReplicate);
-    for (uint64_t tile = P.tile_lo + blockIdx.x; tile < P.tile_hi; tile += gridDim.x) {
+    for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
         const uint32_t m = scan_tile_count(P, tile);
-        const uint32_t k0 = uint32_t(tid) * kScanItems;
-        const uint64_t idx0 = tile * uint64_t(kScanTile) + k0;
-        if (tid == 0) {
+        // exclusive prefix of the tile: segment base (+) in-segment prefix
+        Run2 tile_excl;
+        {
             const int seg = scan_segment_of(P, tile);
-            const double* b = st.segbase + 4 * seg;
-            const double* p = st.prefix + 4 * (tile - P.tile_lo);
-            Run base{dd{__ldcg(b), __ldcg(b + 1)}, dd{__ldcg(b + 2), __ldcg(b + 3)}, 0.0};
-            Run pre{dd{__ldcg(p), __ldcg(p + 1)}, dd{__ldcg(p + 2), __ldcg(p + 3)},
-                    double((tile - P.seg_tile[seg]) * uint64_t(kScanTile))};
-            sm.tile_excl = scan_tile_exclusive(base, pre);
+            const double* bp = st.segbase + 4 * seg;
+            const double* pp = st.prefix + 4 * (tile - P.tile_lo);
+            const Run base{dd{__ldcg(bp), __ldcg(bp + 1)}, dd{__ldcg(bp + 2), __ldcg(bp + 3)}, 0.0};
+            const Run pre{dd{__ldcg(pp), __ldcg(pp + 1)}, dd{__ldcg(pp + 2), __ldcg(pp + 3)},
+                          double((tile - P.seg_tile[seg]) * uint64_t(kScanTile))};
+            tile_excl = scan_tile_exclusive(base, pre);
         }
-        double v[kScanItems], lp[kScanItems], lq[kScanItems];
-        scan_thread_values(f, P, idx0, k0, m, v);
-        scan_thread_local(v, lp, lq);
-        Run2 inc{lp[kScanItems - 1], lq[kScanItems - 1]};
+        Run2 wpre{0.0, 0.0};   // fold of the passes before this one ("warps before mine")
+#pragma unroll 2
+        for (int j = 0; j < kWarps; ++j) {
+            const uint32_t k0 = uint32_t(j * 32 + lane) * kScanItems;
+            const uint64_t idx0 = tile * uint64_t(kScanTile) + k0;
+            double v[kScanItems];
+            scan_thread_values(f, P, idx0, k0, m, v);
+            Run2 inc;
+            {
+                double p = 0.0, q = 0.0;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            Run2 up{__shfl_up_sync(0xffffffffu, inc.p, d), __shfl_up_sync(0xffffffffu, inc.q, d)};
-            if (lane >= d) inc = run2_combine(up, inc, double(kScanItems * d));
-        }
-        if (lane == 31) sm.warp_tot2[warp] = inc;
-        Run2 excl{__shfl_up_sync(0xffffffffu, inc.p, 1), __shfl_up_sync(0xffffffffu, inc.q, 1)};
-        if (lane == 0) excl = Run2{0.0, 0.0};
-        __syncthreads();
-        Run2 wpre{0.0, 0.0};
-        for (int w = 0; w < warp; ++w) wpre = run2_combine(wpre, sm.warp_tot2[w], double(32 * kScanItems));
-        const Run2 et = run2_combine(wpre, excl, double(kScanItems * lane));
-        const Run2 full = run2_combine(sm.tile_excl, et, double(k0));
-        double Pv[kScanItems], Qv[kScanItems];
-#pragma unroll
-        for (int j = 0; j < kScanItems; ++j) {
-            Pv[j] = full.p + lp[j];
-            Qv[j] = fma(double(j + 1), full.p, full.q) + lq[j];
-        }
-        if (k0 + kScanItems <= m) {
-            ptx::st_f64x4(st.P + idx0, Pv[0], Pv[1], Pv[2], Pv[3]);
-            ptx::st_f64x4(st.P + idx0 + 4, Pv[4], Pv[5], Pv[6], Pv[7]);
-            ptx::st_f64x4(st.Q + idx0, Qv[0], Qv[1], Qv[2], Qv[3]);
-            ptx::st_f64x4(st.Q + idx0 + 4, Qv[4], Qv[5], Qv[6], Qv[7]);
-            if (st.samples) {
-                ptx::st_f64x4(st.samples + idx0, v[0], v[1], v[2], v[3]);
-                ptx::st_f64x4(st.samples + idx0 + 4, v[4], v[5], v[6], v[7]);
+                for (int i = 0; i < kScanItems; ++i) p += v[i], q += p;
+                inc = Run2{p, q};
             }
-            if (replicate) {
-                for (int r = 0; r < P.world; ++r) {
-                    if (r == P.rank) continue;
-                    ptx::st_f64x4(st.peerP[r] + idx0, Pv[0], Pv[1], Pv[2], Pv[3]);
-                    ptx::st_f64x4(st.peerP[r] + idx0 + 4, Pv[4], Pv[5], Pv[6], Pv[7]);
-                    ptx::st_f64x4(st.peerQ[r] + idx0, Qv[0], Qv[1], Qv[2], Qv[3]);
-                    ptx::st_f64x4(st.peerQ[r] + idx0 + 4, Qv[4], Qv[5], Qv[6], Qv[7]);
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                Run2 up{__shfl_up_sync(0xffffffffu, inc.p, d), __shfl_up_sync(0xffffffffu, inc.q, d)};
+                if (lane >= d) inc = run2_combine(up, inc, double(kScanItems * d));
+            }
+            const Run2 tot{__shfl_sync(0xffffffffu, inc.p, 31), __shfl_sync(0xffffffffu, inc.q, 31)};
+            Run2 excl{__shfl_up_sync(0xffffffffu, inc.p, 1), __shfl_up_sync(0xffffffffu, inc.q, 1)};
+            if (lane == 0) excl = Run2{0.0, 0.0};
+            const Run2 et = run2_combine(wpre, excl, double(kScanItems * lane));
+            const Run2 full = run2_combine(tile_excl, et, double(k0));
+            wpre = run2_combine(wpre, tot, double(32 * kScanItems));
+            double Pv[kScanItems], Qv[kScanItems];
+            {
+                double p = 0.0, q = 0.0;
+#pragma unroll
+                for (int i = 0; i < kScanItems; ++i) {
+                    p += v[i], q += p;
+                    Pv[i] = full.p + p;
+                    Qv[i] = fma(double(i + 1), full.p, full.q) + q;
                 }
             }
-        } else {
+            if (k0 + kScanItems <= m) {
+                ptx::st_f64x4(st.P + idx0, Pv[0], Pv[1], Pv[2], Pv[3]);
+                ptx::st_f64x4(st.P + idx0 + 4, Pv[4], Pv[5], Pv[6], Pv[7]);
+                ptx::st_f64x4(st.Q + idx0, Qv[0], Qv[1], Qv[2], Qv[3]);
+                ptx::st_f64x4(st.Q + idx0 + 4, Qv[4], Qv[5], Qv[6], Qv[7]);
+                if (st.samples) {
+                    ptx::st_f64x4(st.samples + idx0, v[0], v[1], v[2], v[3]);
+                    ptx::st_f64x4(st.samples + idx0 + 4, v[4], v[5], v[6], v[7]);
+                }
+                if (replicate) {
+                    for (int r = 0; r < P.world; ++r) {
+                        if (r == P.rank) continue;
+                        ptx::st_f64x4(st.peerP[r] + idx0, Pv[0], Pv[1], Pv[2], Pv[3]);
+                        ptx::st_f64x4(st.peerP[r] + idx0 + 4, Pv[4], Pv[5], Pv[6], Pv[7]);
+                        ptx::st_f64x4(st.peerQ[r] + idx0, Qv[0], Qv[1], Qv[2], Qv[3]);
+                        ptx::st_f64x4(st.peerQ[r] + idx0 + 4, Qv[4], Qv[5], Qv[6], Qv[7]);
+                    }
+                }
+            } else {
 #pragma unroll
-            for (int j = 0; j < kScanItems; ++j) {
-                if (k0 + j < m) {
-                    st.P[idx0 + j] = Pv[j];
-                    st.Q[idx0 + j] = Qv[j];
-                    if (st.samples) st.samples[idx0 + j] = v[j];
-                    if (replicate)
-                        for (int r = 0; r < P.world; ++r)
-                            if (r != P.rank) st.peerP[r][idx0 + j] = Pv[j], st.peerQ[r][idx0 + j] = Qv[j];
+                for (int i = 0; i < kScanItems; ++i) {
+                    if (k0 + i < m) {
+                        st.P[idx0 + i] = Pv[i];
+                        st.Q[idx0 + i] = Qv[i];
+                        if (st.samples) st.samples[idx0 + i] = v[i];
+                        if (replicate)
+                            for (int r = 0; r < P.world; ++r)
+                                if (r != P.rank) st.peerP[r][idx0 + i] = Pv[i], st.peerQ[r][idx0 + i] = Qv[i];
+                    }
                 }
             }
-        }
-        // The three scalars the callers print (4main.c:241 uses P[n-2]).
+            // The three scalars the callers print (4main.c:241 uses P[n-2]).
+            if (idx0 + kScanItems + 1 >= P.n && idx0 < P.n) {
 #pragma unroll
-        for (int j = 0; j < kScanItems; ++j) {
-            const uint64_t i = idx0 + j;
-            if (i + 1 == P.n || i + 2 == P.n) {
-                for (int r = 0; r < P.world; ++r) {
-                    double* fin = st.peers[r]->scan_final;
-                    if (i + 1 == P.n) {
-                        ptx::st_relaxed_sys_f64(fin + 0, Pv[j]);
-                        ptx::st_relaxed_sys_f64(fin + 1, Qv[j]);
-                        if (P.n == 1) ptx::st_relaxed_sys_f64(fin + 2, 0.0);
-                    } else {
-                        ptx::st_relaxed_sys_f64(fin + 2, Pv[j]);
+                for (int i = 0; i < kScanItems; ++i) {
+                    const uint64_t g = idx0 + i;
+                    if (g + 1 == P.n || g + 2 == P.n) {
+                        for (int r = 0; r < P.world; ++r) {
+                            double* fin = st.peers[r]->scan_final;
+                            if (g + 1 == P.n) {
+                                ptx::st_relaxed_sys_f64(fin + 0, Pv[i]);
+                                ptx::st_relaxed_sys_f64(fin + 1, Qv[i]);
+                                if (P.n == 1) ptx::st_relaxed_sys_f64(fin + 2, 0.0);
+                            } else {
+                                ptx::st_relaxed_sys_f64(fin + 2, Pv[i]);
+                            }
+                        }
                     }
                 }
             }
         }
-        __syncthreads();
     }
 
     // ---- end: second barrier, result -------------------------------------------
@@ -365,10 +421,19 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(ScanState st) {
         st.ready[1] = gen;             // generation completed
         R->t_end_ns = ptx::globaltimer();
     }
+    // device -> host leg: the result block goes straight into pinned mapped host memory
+    if (st.result_host) {
+        __syncwarp();
+        static_assert(sizeof(bq_scan_result) % 8 == 0 && sizeof(bq_scan_result) / 8 <= 32,
+                      "scan result block = one word per lane");
+        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(st.result);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(st.result_host);
+        if (lane < int(sizeof(bq_scan_result) / 8)) dst[lane] = src[lane];
+    }
 }
 
 template <class F>
-cudaError_t launch_scan_f(const ScanState& st, unsigned grid, cudaStream_t stream) {
+cudaError_t launch_scan_f(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(grid, 1, 1);
     lc.blockDim = dim3(kScanThreads, 1, 1);
@@ -378,7 +443,10 @@ cudaError_t launch_scan_f(const ScanState& st, unsigned grid, cudaStream_t strea
     attr[0].val.cooperative = 1;
     lc.attrs = attr;
     lc.numAttrs = 1;
-    return cudaLaunchKernelEx(&lc, scan_kernel<F>, st);
+    ScanParams prm;
+    prm.P = P;
+    prm.st = st;
+    return cudaLaunchKernelEx(&lc, scan_kernel<F>, prm);
 }
 
 template <class F>
@@ -403,11 +471,11 @@ int scan_max_grid(int /*device*/, int sm_count) {
 
 cudaError_t launch_scan(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
     switch (P.integrand) {
-        case BQ_F_SIN: return launch_scan_f<SinF>(st, grid, stream);
-        case BQ_F_ACC: return launch_scan_f<AccF>(st, grid, stream);
-        case BQ_F_VEL: return launch_scan_f<VelF>(st, grid, stream);
-        case BQ_F_DIS: return launch_scan_f<DisF>(st, grid, stream);
-        case BQ_F_PROFILE: return launch_scan_f<ProfileF>(st, grid, stream);
+        case BQ_F_SIN: return launch_scan_f<SinF>(P, st, grid, stream);
+        case BQ_F_ACC: return launch_scan_f<AccF>(P, st, grid, stream);
+        case BQ_F_VEL: return launch_scan_f<VelF>(P, st, grid, stream);
+        case BQ_F_DIS: return launch_scan_f<DisF>(P, st, grid, stream);
+        case BQ_F_PROFILE: return launch_scan_f<ProfileF>(P, st, grid, stream);
         default: return cudaErrorInvalidValue;
     }
 }

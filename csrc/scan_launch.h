@@ -8,7 +8,7 @@
 namespace bq {
 
 struct ScanState {
-    const ScanPlan* plan;
+    const ScanPlan* plan;     // unused by the kernel (the plan rides in the launch parameters)
     double* agg;              // [rank tiles][2]  tile aggregates (sum v, sum of local P)
     double* prefix;           // [rank tiles][4]  exclusive prefix inside the segment (dd P, dd Q)
     double* segbase;          // [kSegments][4]   exclusive prefix of each segment (dd P, dd Q)
@@ -16,6 +16,7 @@ struct ScanState {
     unsigned int* ticket_a;
     unsigned int* ticket_b;
     bq_scan_result* result;
+    bq_scan_result* result_host;   // pinned host block as mapped on this device (or null)
     CommBlock* comm;
     CommBlock* peers[BQ_MAX_WORLD];
     const double* table;
