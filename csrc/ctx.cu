@@ -3,8 +3,9 @@
 // The reference's host side is three main()s that cudaMalloc/cudaMemcpy 144 MB
 // of uninitialised memory per run and never check an error
 // (cintegrate.cu:111-133).  Here one context per device owns every buffer for
-// its lifetime; a call moves sizeof(Plan) bytes down and sizeof(bq_result)
-// bytes up, both through pinned memory, around exactly one kernel launch.
+// its lifetime; a call is exactly one kernel launch: the plan rides down in
+// the launch's parameter buffer and the kernel writes the result block into
+// pinned, mapped host memory itself.
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -74,7 +75,6 @@ int bq_ctx_create(int device, bq_ctx** out) {
     BQ_CUDA(cudaEventCreate(&c->ev0));
     BQ_CUDA(cudaEventCreate(&c->ev1));
 
-    BQ_CUDA(cudaMalloc(&c->d_plans, sizeof(PlanSlot) * kRing));
     BQ_CUDA(cudaMalloc(&c->d_partials, sizeof(dd) * kChunks));
     BQ_CUDA(cudaMemset(c->d_partials, 0, sizeof(dd) * kChunks));
     BQ_CUDA(cudaMalloc(&c->d_ticket, 256));
@@ -89,16 +89,12 @@ int bq_ctx_create(int device, bq_ctx** out) {
     BQ_CUDA(cudaMemset(c->d_table, 0, sizeof(double) * (kMaxTable + 2)));
     BQ_CUDA(cudaMalloc(&c->d_seg_scratch, sizeof(double) * 2 * kSegments));
 
-    BQ_CUDA(cudaHostAlloc(&c->h_plans, sizeof(PlanSlot) * kRing, cudaHostAllocDefault));
     BQ_CUDA(cudaHostAlloc(&c->h_result, sizeof(bq_result), cudaHostAllocMapped));
     BQ_CUDA(cudaHostGetDevicePointer((void**)&c->h_result_dev, c->h_result, 0));
-    BQ_CUDA(cudaHostAlloc(&c->h_scan_result, sizeof(bq_scan_result), cudaHostAllocDefault));
+    BQ_CUDA(cudaHostAlloc(&c->h_scan_result, sizeof(bq_scan_result), cudaHostAllocMapped));
+    BQ_CUDA(cudaHostGetDevicePointer((void**)&c->h_scan_result_dev, c->h_scan_result, 0));
     memset(c->h_result, 0, sizeof(bq_result));
     memset(c->h_scan_result, 0, sizeof(bq_scan_result));
-    for (int i = 0; i < kRing; ++i) {
-        BQ_CUDA(cudaEventCreateWithFlags(&c->ring_ev[i], cudaEventDisableTiming));
-        c->ring_busy[i] = false;
-    }
     for (int r = 0; r < BQ_MAX_WORLD; ++r) c->peers[r] = nullptr, c->peer_ipc[r] = false;
     c->peers[0] = c->d_comm;
 
@@ -120,7 +116,6 @@ void bq_ctx_destroy(bq_ctx* c) {
     for (int r = 0; r < BQ_MAX_WORLD; ++r)
         if (c->peer_ipc[r] && c->peers[r]) cudaIpcCloseMemHandle(c->peers[r]);
     scan_ctx_free(c);
-    cudaFree(c->d_plans);
     cudaFree(c->d_partials);
     cudaFree(c->d_ticket);
     cudaFree(c->d_result);
@@ -129,10 +124,8 @@ void bq_ctx_destroy(bq_ctx* c) {
     cudaFree(c->d_table);
     cudaFree(c->d_seg_scratch);
     cudaFree(c->d_trace);
-    cudaFreeHost(c->h_plans);
     cudaFreeHost(c->h_result);
     cudaFreeHost(c->h_scan_result);
-    for (int i = 0; i < kRing; ++i) cudaEventDestroy(c->ring_ev[i]);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -212,24 +205,6 @@ int bq_ctx_inject_fault(bq_ctx* c, int kind) {
 }  // extern "C"
 
 namespace bq {
-
-// Claims the next staging slot (waiting for its previous use to drain).
-int ring_acquire(bq_ctx* c, int* slot) {
-    const int s = c->ring_head;
-    c->ring_head = (c->ring_head + 1) % kRing;
-    if (c->ring_busy[s]) {
-        BQ_CUDA(cudaEventSynchronize(c->ring_ev[s]));
-        c->ring_busy[s] = false;
-    }
-    *slot = s;
-    return BQ_OK;
-}
-
-int ring_release(bq_ctx* c, int slot, cudaStream_t stream) {
-    BQ_CUDA(cudaEventRecord(c->ring_ev[slot], stream));
-    c->ring_busy[slot] = true;
-    return BQ_OK;
-}
 
 static LaunchConfig quad_config(const bq_ctx* c, const Plan& P) {
     LaunchConfig cfg;

@@ -10,18 +10,6 @@
 
 namespace bq {
 
-constexpr int kRing = 64;   // pinned / device parameter slots in flight
-
-union PlanSlot {
-    Plan quad;
-    ScanPlan scan;
-    unsigned char raw[512];
-};
-static_assert(sizeof(Plan) <= 512 && sizeof(ScanPlan) <= 512, "PlanSlot too small");
-
-int ring_acquire(struct ::bq_ctx* c, int* slot);
-int ring_release(struct ::bq_ctx* c, int slot, cudaStream_t stream);
-
 }  // namespace bq
 
 struct bq_ctx {
@@ -40,7 +28,6 @@ struct bq_ctx {
     uint32_t fault_flags = 0;
 
     // device buffers (allocated once)
-    bq::PlanSlot* d_plans = nullptr;
     bq::dd* d_partials = nullptr;
     unsigned int* d_ticket = nullptr;     // [0] quad, [8] scan phase A, [16] scan phase B
     bq_result* d_result = nullptr;
@@ -63,13 +50,10 @@ struct bq_ctx {
     int scan_grid = 0;
 
     // pinned staging
-    bq::PlanSlot* h_plans = nullptr;
     bq_result* h_result = nullptr;
     bq_result* h_result_dev = nullptr;    // h_result as the device addresses it (mapped)
     bq_scan_result* h_scan_result = nullptr;
-    cudaEvent_t ring_ev[bq::kRing];
-    bool ring_busy[bq::kRing];
-    int ring_head = 0;
+    bq_scan_result* h_scan_result_dev = nullptr;
 
     // world
     int rank = 0, world = 1;

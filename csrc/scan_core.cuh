@@ -59,9 +59,12 @@ BQ_HDI int scan_segment_of(const ScanPlan& P, uint64_t tile) {
 template <class F>
 BQ_HD void scan_thread_values(const F& f, const ScanPlan& P, uint64_t first_idx, uint32_t k0,
                               uint32_t m, double (&v)[kScanItems]) {
+    // One integer -> double conversion per run; base + j is exact below 2^53, so
+    // this is double(first_idx + j) bit for bit.
+    const double base = double(first_idx);
 #pragma unroll
     for (int j = 0; j < kScanItems; ++j) {
-        const double x = fma(double(first_idx + uint64_t(j)), P.dx, P.x0);
+        const double x = fma(base + double(j), P.dx, P.x0);
         v[j] = (k0 + uint32_t(j) < m) ? f.template eval<double>(x) : 0.0;
     }
 }
@@ -71,10 +74,13 @@ BQ_HD void scan_thread_aggregate(const double (&v)[kScanItems], uint32_t k0, uin
                                  double& w) {
     s = 0.0;
     w = 0.0;
+    // weights m-k0, m-k0-1, ... as exact doubles (one conversion per run); a
+    // sample past the end of the grid has v == 0 and weight 0
+    const double w0 = double(int32_t(m) - int32_t(k0));
 #pragma unroll
     for (int j = 0; j < kScanItems; ++j) {
-        const uint32_t k = k0 + uint32_t(j);
-        const double wt = k < m ? double(m - k) : 0.0;
+        const double wj = w0 - double(j);
+        const double wt = wj > 0.0 ? wj : 0.0;
         s += v[j];
         w = fma(v[j], wt, w);
     }

@@ -73,11 +73,10 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
         set_error("cumulative: output buffers must be 32-byte aligned");
         return BQ_ERR_INVALID;
     }
-    int slot = 0;
-    int rc = ring_acquire(c, &slot);
-    if (rc != BQ_OK) return rc;
-    ScanPlan* hp = &c->h_plans[slot].scan;
-    rc = make_scan_plan(*job, rank, world, c->table_len, hp);
+    // The plan travels in the kernel parameter buffer: no staging copy.
+    ScanPlan plan;
+    ScanPlan* hp = &plan;
+    int rc = make_scan_plan(*job, rank, world, c->table_len, hp);
     if (rc != BQ_OK) return rc;
     hp->timeout_ms = c->timeout_ms;
     if (c->fault_flags) hp->flags |= kScanSkipPublish;
@@ -97,12 +96,9 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
     }
     rc = scan_reserve(c, hp->tile_hi - hp->tile_lo);
     if (rc != BQ_OK) return rc;
-    ScanPlan* dp = &c->d_plans[slot].scan;
-    BQ_CUDA(cudaMemcpyAsync(dp, hp, sizeof(ScanPlan), cudaMemcpyHostToDevice, stream));
 
     ScanState st;
     memset(&st, 0, sizeof(st));
-    st.plan = dp;
     st.agg = c->d_scan_agg;
     st.prefix = c->d_scan_prefix;
     st.segbase = c->d_scan_misc;
@@ -110,6 +106,7 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
     st.ticket_a = c->d_ticket + 8;
     st.ticket_b = c->d_ticket + 16;
     st.result = c->d_scan_result;
+    st.result_host = c->h_scan_result_dev;   // the kernel itself writes the result block to the host
     st.comm = c->d_comm;
     for (int r = 0; r < BQ_MAX_WORLD; ++r) st.peers[r] = c->peers[r];
     st.peers[rank] = c->d_comm;
@@ -130,10 +127,8 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
     if (tiles < grid) grid = unsigned(tiles ? tiles : 1);
     BQ_CUDA(launch_scan(*hp, st, grid, stream));
     c->launches += 1;
-    BQ_CUDA(cudaMemcpyAsync(c->h_scan_result, c->d_scan_result, sizeof(bq_scan_result),
-                            cudaMemcpyDeviceToHost, stream));
     c->last_stream = stream;
-    return ring_release(c, slot, stream);
+    return BQ_OK;
 }
 
 }  // namespace bq

@@ -28,6 +28,7 @@
 // CTAs of one launch wait on each other, so the grid never exceeds what is
 // co-resident (cooperative launch attribute).
 #include <cuda_runtime.h>
+#include <stdlib.h>
 
 #include <type_traits>
 
@@ -121,13 +122,9 @@ struct ScanParams {
     ScanState st;
 };
 
-// (a0 .. a7) summed in the order of an 8-lane xor butterfly (offsets 4, 2, 1).
-__device__ __forceinline__ double butterfly8(const double (&a)[8]) {
-    return ((a[0] + a[4]) + (a[2] + a[6])) + ((a[1] + a[5]) + (a[3] + a[7]));
-}
-
-template <class F>
-__global__ void __launch_bounds__(kScanThreads, 4) scan_kernel(const __grid_constant__ ScanParams prm) {
+// MINB = resident CTAs per SM the register budget is cut for (4: 64 registers, 3: 80, 2: 128).
+template <class F, int MINB>
+__global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_constant__ ScanParams prm) {
     const ScanPlan& P = prm.P;
     const ScanState& st = prm.st;
     __shared__ ScanSmem sm;
@@ -164,18 +161,32 @@ __global__ void __launch_bounds__(kScanThreads, 4) scan_kernel(const __grid_cons
     // ---- phase A: tile aggregates, one warp per tile ---------------------------
     for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
         const uint32_t m = scan_tile_count(P, tile);
-        double a[kWarps], b[kWarps];
-#pragma unroll
-        for (int j = 0; j < kWarps; ++j) {   // pass j = the samples of "warp j" of a block scan
+        // pass j = the samples of "warp j" of a block scan; the 8 pass sums are
+        // folded in the order of an 8-lane xor butterfly: ((0+4)+(2+6)) + ((1+5)+(3+7))
+        auto pass = [&](int j, double& s_out, double& w_out) {
             const uint32_t k0 = uint32_t(j * 32 + lane) * kScanItems;
             double v[kScanItems];
             scan_thread_values(f, P, tile * uint64_t(kScanTile) + k0, k0, m, v);
             double s, w;
             scan_thread_aggregate(v, k0, m, s, w);
-            a[j] = warp_sum(s);
-            b[j] = warp_sum(w);
-        }
-        if (lane == 0) ptx::st_f64x2(st.agg + 2 * (tile - P.tile_lo), butterfly8(a), butterfly8(b));
+            s_out = warp_sum(s);
+            w_out = warp_sum(w);
+        };
+        auto pair = [&](int j, double& s_out, double& w_out) {
+            double s0, w0, s1, w1;
+            pass(j, s0, w0);
+            pass(j + 4, s1, w1);
+            s_out = s0 + s1;
+            w_out = w0 + w1;
+        };
+        double sa, wa, sb, wb, sc, wc, sd, wd;
+        pair(0, sa, wa);
+        pair(2, sb, wb);
+        sa += sb, wa += wb;
+        pair(1, sc, wc);
+        pair(3, sd, wd);
+        sc += sd, wc += wd;
+        if (lane == 0) ptx::st_f64x2(st.agg + 2 * (tile - P.tile_lo), sa + sc, wa + wc);
     }
     __syncthreads();
     if (tid == 0) {
@@ -298,7 +309,7 @@ __global__ void __launch_bounds__(kScanThreads, 4) scan_kernel(const __grid_cons
             tile_excl = scan_tile_exclusive(base, pre);
         }
         Run2 wpre{0.0, 0.0};   // fold of the passes before this one ("warps before mine")
-#pragma unroll 2
+#pragma unroll 1
         for (int j = 0; j < kWarps; ++j) {
             const uint32_t k0 = uint32_t(j * 32 + lane) * kScanItems;
             const uint64_t idx0 = tile * uint64_t(kScanTile) + k0;
@@ -322,61 +333,61 @@ __global__ void __launch_bounds__(kScanThreads, 4) scan_kernel(const __grid_cons
             const Run2 et = run2_combine(wpre, excl, double(kScanItems * lane));
             const Run2 full = run2_combine(tile_excl, et, double(k0));
             wpre = run2_combine(wpre, tot, double(32 * kScanItems));
-            double Pv[kScanItems], Qv[kScanItems];
-            {
+            const bool has_final = idx0 + kScanItems + 1 >= P.n && idx0 < P.n;   // P[n-1] / P[n-2] live here
+            if (k0 + kScanItems <= m && !has_final) {
+                // fast path: a full run of 8 samples, stored as 2 x 256 bits per table
                 double p = 0.0, q = 0.0;
 #pragma unroll
-                for (int i = 0; i < kScanItems; ++i) {
-                    p += v[i], q += p;
-                    Pv[i] = full.p + p;
-                    Qv[i] = fma(double(i + 1), full.p, full.q) + q;
+                for (int half = 0; half < 2; ++half) {
+                    double Ph[4], Qh[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int ii = half * 4 + i;
+                        p += v[ii], q += p;
+                        Ph[i] = full.p + p;
+                        Qh[i] = fma(double(ii + 1), full.p, full.q) + q;
+                    }
+                    ptx::st_f64x4(st.P + idx0 + 4 * half, Ph[0], Ph[1], Ph[2], Ph[3]);
+                    ptx::st_f64x4(st.Q + idx0 + 4 * half, Qh[0], Qh[1], Qh[2], Qh[3]);
+                    if (replicate) {
+                        for (int r = 0; r < P.world; ++r) {
+                            if (r == P.rank) continue;
+                            ptx::st_f64x4(st.peerP[r] + idx0 + 4 * half, Ph[0], Ph[1], Ph[2], Ph[3]);
+                            ptx::st_f64x4(st.peerQ[r] + idx0 + 4 * half, Qh[0], Qh[1], Qh[2], Qh[3]);
+                        }
+                    }
                 }
-            }
-            if (k0 + kScanItems <= m) {
-                ptx::st_f64x4(st.P + idx0, Pv[0], Pv[1], Pv[2], Pv[3]);
-                ptx::st_f64x4(st.P + idx0 + 4, Pv[4], Pv[5], Pv[6], Pv[7]);
-                ptx::st_f64x4(st.Q + idx0, Qv[0], Qv[1], Qv[2], Qv[3]);
-                ptx::st_f64x4(st.Q + idx0 + 4, Qv[4], Qv[5], Qv[6], Qv[7]);
                 if (st.samples) {
                     ptx::st_f64x4(st.samples + idx0, v[0], v[1], v[2], v[3]);
                     ptx::st_f64x4(st.samples + idx0 + 4, v[4], v[5], v[6], v[7]);
                 }
-                if (replicate) {
-                    for (int r = 0; r < P.world; ++r) {
-                        if (r == P.rank) continue;
-                        ptx::st_f64x4(st.peerP[r] + idx0, Pv[0], Pv[1], Pv[2], Pv[3]);
-                        ptx::st_f64x4(st.peerP[r] + idx0 + 4, Pv[4], Pv[5], Pv[6], Pv[7]);
-                        ptx::st_f64x4(st.peerQ[r] + idx0, Qv[0], Qv[1], Qv[2], Qv[3]);
-                        ptx::st_f64x4(st.peerQ[r] + idx0 + 4, Qv[4], Qv[5], Qv[6], Qv[7]);
-                    }
-                }
             } else {
+                // ragged end of the grid, and the run that holds the final scalars
+                double p = 0.0, q = 0.0;
 #pragma unroll
                 for (int i = 0; i < kScanItems; ++i) {
+                    p += v[i], q += p;
+                    const double Pi = full.p + p;
+                    const double Qi = fma(double(i + 1), full.p, full.q) + q;
+                    const uint64_t g = idx0 + i;
                     if (k0 + i < m) {
-                        st.P[idx0 + i] = Pv[i];
-                        st.Q[idx0 + i] = Qv[i];
-                        if (st.samples) st.samples[idx0 + i] = v[i];
+                        st.P[g] = Pi;
+                        st.Q[g] = Qi;
+                        if (st.samples) st.samples[g] = v[i];
                         if (replicate)
                             for (int r = 0; r < P.world; ++r)
-                                if (r != P.rank) st.peerP[r][idx0 + i] = Pv[i], st.peerQ[r][idx0 + i] = Qv[i];
+                                if (r != P.rank) st.peerP[r][g] = Pi, st.peerQ[r][g] = Qi;
                     }
-                }
-            }
-            // The three scalars the callers print (4main.c:241 uses P[n-2]).
-            if (idx0 + kScanItems + 1 >= P.n && idx0 < P.n) {
-#pragma unroll
-                for (int i = 0; i < kScanItems; ++i) {
-                    const uint64_t g = idx0 + i;
+                    // The three scalars the callers print (4main.c:241 uses P[n-2]).
                     if (g + 1 == P.n || g + 2 == P.n) {
                         for (int r = 0; r < P.world; ++r) {
                             double* fin = st.peers[r]->scan_final;
                             if (g + 1 == P.n) {
-                                ptx::st_relaxed_sys_f64(fin + 0, Pv[i]);
-                                ptx::st_relaxed_sys_f64(fin + 1, Qv[i]);
+                                ptx::st_relaxed_sys_f64(fin + 0, Pi);
+                                ptx::st_relaxed_sys_f64(fin + 1, Qi);
                                 if (P.n == 1) ptx::st_relaxed_sys_f64(fin + 2, 0.0);
                             } else {
-                                ptx::st_relaxed_sys_f64(fin + 2, Pv[i]);
+                                ptx::st_relaxed_sys_f64(fin + 2, Pi);
                             }
                         }
                     }
@@ -432,8 +443,19 @@ __global__ void __launch_bounds__(kScanThreads, 4) scan_kernel(const __grid_cons
     }
 }
 
-template <class F>
-cudaError_t launch_scan_f(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
+// Resident CTAs per SM the scan runs with.  3 by default (measured best on B200);
+// B200QUAD_SCAN_CTAS=2|3|4 overrides it for tuning runs.
+int scan_ctas_per_sm() {
+    static int v = [] {
+        const char* e = getenv("B200QUAD_SCAN_CTAS");
+        const int k = e ? atoi(e) : 0;
+        return (k >= 2 && k <= 4) ? k : 3;
+    }();
+    return v;
+}
+
+template <class F, int MINB>
+cudaError_t launch_scan_fm(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(grid, 1, 1);
     lc.blockDim = dim3(kScanThreads, 1, 1);
@@ -446,17 +468,35 @@ cudaError_t launch_scan_f(const ScanPlan& P, const ScanState& st, unsigned grid,
     ScanParams prm;
     prm.P = P;
     prm.st = st;
-    return cudaLaunchKernelEx(&lc, scan_kernel<F>, prm);
+    return cudaLaunchKernelEx(&lc, scan_kernel<F, MINB>, prm);
 }
 
 template <class F>
-int occupancy_f() {
+cudaError_t launch_scan_f(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
+    switch (scan_ctas_per_sm()) {
+        case 2: return launch_scan_fm<F, 2>(P, st, grid, stream);
+        case 4: return launch_scan_fm<F, 4>(P, st, grid, stream);
+        default: return launch_scan_fm<F, 3>(P, st, grid, stream);
+    }
+}
+
+template <class F, int MINB>
+int occupancy_fm() {
     int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_kernel<F>, kScanThreads, 0) != cudaSuccess) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_kernel<F, MINB>, kScanThreads, 0) != cudaSuccess) {
         cudaGetLastError();
         return 1;
     }
     return n < 1 ? 1 : n;
+}
+
+template <class F>
+int occupancy_f() {
+    switch (scan_ctas_per_sm()) {
+        case 2: return occupancy_fm<F, 2>();
+        case 4: return occupancy_fm<F, 4>();
+        default: return occupancy_fm<F, 3>();
+    }
 }
 
 }  // namespace
@@ -465,7 +505,7 @@ int scan_max_grid(int /*device*/, int sm_count) {
     int occ = occupancy_f<ProfileF>();
     const int o2 = occupancy_f<DisF>();
     if (o2 < occ) occ = o2;
-    if (occ > 4) occ = 4;
+    if (occ > scan_ctas_per_sm()) occ = scan_ctas_per_sm();
     return occ * sm_count;
 }
 
