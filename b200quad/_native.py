@@ -127,7 +127,8 @@ def load():
     global _lib, _is_cuda, _load_note
     if _lib is not None:
         return _lib, _is_cuda
-    cuda_path = os.path.join(_LIBDIR, "libb200quad.so")
+    # B200QUAD_LIB: load another build of the core library (tuning runs compare variants)
+    cuda_path = os.environ.get("B200QUAD_LIB") or os.path.join(_LIBDIR, "libb200quad.so")
     cpu_path = os.path.join(_LIBDIR, "libb200quad_cpu.so")
     if not os.path.exists(cuda_path) and not os.path.exists(cpu_path):
         raise NativeError("native libraries are not built: run `python build.py` "

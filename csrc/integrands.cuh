@@ -15,6 +15,7 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "bq_dd.cuh"
 
@@ -78,6 +79,8 @@ struct ProfileF {
     double inv_dx;
     template <class R>
     BQ_HD R eval(R x) const {
+        // (int)u / R(i): measured on B200, these two conversions are cheaper than any
+        // conversion-free floor built from fp64 adds (the fp64 pipe is the bound here).
         R u = x * R(inv_dx);
         int i = (int)u;
         i = i < 0 ? 0 : (i > len - 2 ? len - 2 : i);

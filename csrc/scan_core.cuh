@@ -74,13 +74,10 @@ BQ_HD void scan_thread_aggregate(const double (&v)[kScanItems], uint32_t k0, uin
                                  double& w) {
     s = 0.0;
     w = 0.0;
-    // weights m-k0, m-k0-1, ... as exact doubles (one conversion per run); a
-    // sample past the end of the grid has v == 0 and weight 0
-    const double w0 = double(int32_t(m) - int32_t(k0));
 #pragma unroll
     for (int j = 0; j < kScanItems; ++j) {
-        const double wj = w0 - double(j);
-        const double wt = wj > 0.0 ? wj : 0.0;
+        const uint32_t k = k0 + uint32_t(j);
+        const double wt = k < m ? double(m - k) : 0.0;
         s += v[j];
         w = fma(v[j], wt, w);
     }
