@@ -62,10 +62,18 @@ BQ_HD void scan_thread_values(const F& f, const ScanPlan& P, uint64_t first_idx,
     // One integer -> double conversion per run; base + j is exact below 2^53, so
     // this is double(first_idx + j) bit for bit.
     const double base = double(first_idx);
+    if (k0 + uint32_t(kScanItems) <= m) {
+        // The whole run lies inside the grid (every run but those of the last tile):
+        // straight-line code, so the kScanItems evaluations overlap.  A per-sample
+        // guard here turns into one branch per sample and serialises them.
 #pragma unroll
-    for (int j = 0; j < kScanItems; ++j) {
-        const double x = fma(base + double(j), P.dx, P.x0);
-        v[j] = (k0 + uint32_t(j) < m) ? f.template eval<double>(x) : 0.0;
+        for (int j = 0; j < kScanItems; ++j) v[j] = f.template eval<double>(fma(base + double(j), P.dx, P.x0));
+    } else {
+#pragma unroll
+        for (int j = 0; j < kScanItems; ++j) {
+            const double x = fma(base + double(j), P.dx, P.x0);
+            v[j] = (k0 + uint32_t(j) < m) ? f.template eval<double>(x) : 0.0;
+        }
     }
 }
 

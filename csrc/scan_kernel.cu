@@ -89,10 +89,22 @@ __device__ void segment_prefixes(const ScanPlan& P, const ScanState& st, int seg
     const uint64_t lo = t0 + uint64_t(tid) * B < t1 ? t0 + uint64_t(tid) * B : t1;
     const uint64_t hi = lo + B < t1 ? lo + B : t1;
 
+    // Both sequential folds below read their tile aggregates in batches: the loads
+    // of a batch are all in flight before the first dependent dd combine, instead
+    // of one L2 round trip per tile on the critical path.
+    constexpr int kBatch = 8;
     Run mine = run_identity();
-    for (uint64_t t = lo; t < hi; ++t) {
-        const double* a = st.agg + 2 * (t - P.tile_lo);
-        mine = run_combine(mine, run_from_tile(__ldcg(a), __ldcg(a + 1), double(scan_tile_count(P, t))));
+    for (uint64_t t = lo; t < hi; t += kBatch) {
+        double s[kBatch], w[kBatch];
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k) {
+            const uint64_t tt = t + k < hi ? t + k : hi - 1;
+            const double* a = st.agg + 2 * (tt - P.tile_lo);
+            s[k] = __ldcg(a), w[k] = __ldcg(a + 1);
+        }
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k)
+            if (t + k < hi) mine = run_combine(mine, run_from_tile(s[k], w[k], double(scan_tile_count(P, t + k))));
     }
     Run inc = mine;
 #pragma unroll
@@ -107,11 +119,22 @@ __device__ void segment_prefixes(const ScanPlan& P, const ScanState& st, int seg
     Run wpre = run_identity();
     for (int w = 0; w < warp; ++w) wpre = run_combine(wpre, sm.warp_tot[w]);
     Run running = run_combine(wpre, excl);
-    for (uint64_t t = lo; t < hi; ++t) {
-        double* o = st.prefix + 4 * (t - P.tile_lo);
-        o[0] = running.p.hi, o[1] = running.p.lo, o[2] = running.q.hi, o[3] = running.q.lo;
-        const double* a = st.agg + 2 * (t - P.tile_lo);
-        running = run_combine(running, run_from_tile(__ldcg(a), __ldcg(a + 1), double(scan_tile_count(P, t))));
+    for (uint64_t t = lo; t < hi; t += kBatch) {
+        double s[kBatch], w[kBatch];
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k) {
+            const uint64_t tt = t + k < hi ? t + k : hi - 1;
+            const double* a = st.agg + 2 * (tt - P.tile_lo);
+            s[k] = __ldcg(a), w[k] = __ldcg(a + 1);
+        }
+#pragma unroll
+        for (int k = 0; k < kBatch; ++k) {
+            if (t + k < hi) {
+                double* o = st.prefix + 4 * (t + k - P.tile_lo);
+                ptx::st_f64x4(o, running.p.hi, running.p.lo, running.q.hi, running.q.lo);
+                running = run_combine(running, run_from_tile(s[k], w[k], double(scan_tile_count(P, t + k))));
+            }
+        }
     }
     if (tid == kScanThreads - 1) sm.seg_tot[seg] = running;
     __syncthreads();
@@ -443,13 +466,14 @@ __global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_c
     }
 }
 
-// Resident CTAs per SM the scan runs with.  3 by default (measured best on B200);
-// B200QUAD_SCAN_CTAS=2|3|4 overrides it for tuning runs.
+// Resident CTAs per SM the scan runs with.  2 by default (measured best on B200: 126
+// registers let the compiler overlap the passes of a tile; 3 and 4 CTAs trade that for
+// occupancy and lose); B200QUAD_SCAN_CTAS=2|3|4 overrides it for tuning runs.
 int scan_ctas_per_sm() {
     static int v = [] {
         const char* e = getenv("B200QUAD_SCAN_CTAS");
         const int k = e ? atoi(e) : 0;
-        return (k >= 2 && k <= 4) ? k : 3;
+        return (k >= 2 && k <= 4) ? k : 2;
     }();
     return v;
 }
@@ -474,9 +498,9 @@ cudaError_t launch_scan_fm(const ScanPlan& P, const ScanState& st, unsigned grid
 template <class F>
 cudaError_t launch_scan_f(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
     switch (scan_ctas_per_sm()) {
-        case 2: return launch_scan_fm<F, 2>(P, st, grid, stream);
         case 4: return launch_scan_fm<F, 4>(P, st, grid, stream);
-        default: return launch_scan_fm<F, 3>(P, st, grid, stream);
+        case 3: return launch_scan_fm<F, 3>(P, st, grid, stream);
+        default: return launch_scan_fm<F, 2>(P, st, grid, stream);
     }
 }
 
@@ -493,9 +517,9 @@ int occupancy_fm() {
 template <class F>
 int occupancy_f() {
     switch (scan_ctas_per_sm()) {
-        case 2: return occupancy_fm<F, 2>();
         case 4: return occupancy_fm<F, 4>();
-        default: return occupancy_fm<F, 3>();
+        case 3: return occupancy_fm<F, 3>();
+        default: return occupancy_fm<F, 2>();
     }
 }
 
