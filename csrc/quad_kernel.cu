@@ -40,9 +40,9 @@
 namespace bq {
 
 template <class R>
-constexpr int rot_unroll() {
-    return sizeof(R) == 8 ? BQ_ROT_UNROLL : BQ_ROT_UNROLL_F32;
-}
+struct RotUnroll {
+    static constexpr int value = sizeof(R) == 8 ? BQ_ROT_UNROLL : BQ_ROT_UNROLL_F32;
+};
 
 template <class R>
 struct Vec2;
@@ -169,7 +169,7 @@ struct PartWorker {
                                                 TileAcc<R>& acc, Vec2<R>& sc, double& x0) const {
         sc = sc_row[0];
         x0 = F::kNeedX ? x0_row[0] : 0.0;
-        constexpr int kUnroll = rot_unroll<R>();
+        constexpr int kUnroll = RotUnroll<R>::value;
 #pragma unroll kUnroll
         for (Count r = 0; r < nrows; ++r) {
             const Vec2<R> sc_next = sc_row[r + 1];
