@@ -108,20 +108,26 @@ struct CpuScan {
 
     void tile_aggregate(uint64_t tile) {
         const uint32_t m = scan_tile_count(P, tile);
-        double ws[kScanThreads / 32], ww[kScanThreads / 32];
-        for (int w = 0; w < kScanThreads / 32; ++w) {
-            double ls[32], lw[32];
+        // thread (pass w, lane l) -> per-lane fold over the 8 passes in the order
+        // ((0+4)+(2+6)) + ((1+5)+(3+7)) -> xor butterfly over the 32 lanes
+        constexpr int kPasses = kScanThreads / 32;
+        static_assert(kPasses == 8, "the pass fold below is written for 8 passes");
+        double ps[kPasses][32], pw[kPasses][32];
+        for (int w = 0; w < kPasses; ++w) {
             for (int l = 0; l < 32; ++l) {
                 const uint32_t k0 = uint32_t(w * 32 + l) * kScanItems;
                 double v[kScanItems];
                 scan_thread_values(f, P, tile * uint64_t(kScanTile) + k0, k0, m, v);
-                scan_thread_aggregate(v, k0, m, ls[l], lw[l]);
+                scan_thread_aggregate(v, k0, m, ps[w][l], pw[w][l]);
             }
-            ws[w] = lanes_sum(ls, 32);
-            ww[w] = lanes_sum(lw, 32);
         }
-        agg[2 * tile] = lanes_sum(ws, 8);
-        agg[2 * tile + 1] = lanes_sum(ww, 8);
+        double ls[32], lw[32];
+        for (int l = 0; l < 32; ++l) {
+            ls[l] = ((ps[0][l] + ps[4][l]) + (ps[2][l] + ps[6][l])) + ((ps[1][l] + ps[5][l]) + (ps[3][l] + ps[7][l]));
+            lw[l] = ((pw[0][l] + pw[4][l]) + (pw[2][l] + pw[6][l])) + ((pw[1][l] + pw[5][l]) + (pw[3][l] + pw[7][l]));
+        }
+        agg[2 * tile] = lanes_sum(ls, 32);
+        agg[2 * tile + 1] = lanes_sum(lw, 32);
     }
 
     Run tile_run(uint64_t t) const {

@@ -42,6 +42,7 @@ namespace bq {
 namespace {
 
 constexpr int kWarps = kScanThreads / 32;
+constexpr size_t kScanStageBytes = size_t(kWarps) * 2 * 32 * kScanItems * sizeof(double);   // 32 KB
 
 struct ScanSmem {
     Run warp_tot[kWarps];
@@ -145,9 +146,12 @@ struct ScanParams {
     ScanState st;
 };
 
-// MINB = resident CTAs per SM the register budget is cut for (4: 64 registers, 3: 80, 2: 128).
-template <class F, int MINB>
-__global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_constant__ ScanParams prm) {
+// Two resident CTAs per SM (128 registers): measured best on B200 — the register room lets
+// the compiler overlap the passes of a tile; 3 and 4 CTAs/SM (80 / 64 registers) both lost.
+// REPL = the fused all-gather (replicate) is compiled in; a separate instantiation so the
+// single-GPU / slice-only kernel carries none of its registers or staging.
+template <class F, bool REPL>
+__global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_constant__ ScanParams prm) {
     const ScanPlan& P = prm.P;
     const ScanState& st = prm.st;
     __shared__ ScanSmem sm;
@@ -184,16 +188,14 @@ __global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_c
     // ---- phase A: tile aggregates, one warp per tile ---------------------------
     for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
         const uint32_t m = scan_tile_count(P, tile);
-        // pass j = the samples of "warp j" of a block scan; the 8 pass sums are
-        // folded in the order of an 8-lane xor butterfly: ((0+4)+(2+6)) + ((1+5)+(3+7))
+        // pass j = the samples of "warp j" of a block scan; each lane folds its 8 pass
+        // shares in the order ((0+4)+(2+6)) + ((1+5)+(3+7)), the 32 lanes then meet in
+        // one xor butterfly (scan tree of cpu_scan.cpp: tile_aggregate)
         auto pass = [&](int j, double& s_out, double& w_out) {
             const uint32_t k0 = uint32_t(j * 32 + lane) * kScanItems;
             double v[kScanItems];
             scan_thread_values(f, P, tile * uint64_t(kScanTile) + k0, k0, m, v);
-            double s, w;
-            scan_thread_aggregate(v, k0, m, s, w);
-            s_out = warp_sum(s);
-            w_out = warp_sum(w);
+            scan_thread_aggregate(v, k0, m, s_out, w_out);   // this lane's share of the pass
         };
         auto pair = [&](int j, double& s_out, double& w_out) {
             double s0, w0, s1, w1;
@@ -209,7 +211,9 @@ __global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_c
         pair(1, sc, wc);
         pair(3, sd, wd);
         sc += sd, wc += wd;
-        if (lane == 0) ptx::st_f64x2(st.agg + 2 * (tile - P.tile_lo), sa + sc, wa + wc);
+        // the lane's 8 pass shares are folded first, then ONE butterfly per tile
+        const double S = warp_sum(sa + sc), W = warp_sum(wa + wc);
+        if (lane == 0) ptx::st_f64x2(st.agg + 2 * (tile - P.tile_lo), S, W);
     }
     __syncthreads();
     if (tid == 0) {
@@ -317,7 +321,9 @@ __global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_c
     __syncthreads();
 
     // ---- phase B: scan + store, one warp per tile --------------------------------
-    const bool replicate = multi && (P.flags & kScanReplicate);
+    const bool replicate = REPL && multi && (P.flags & kScanReplicate);
+    extern __shared__ __align__(32) double sStage[];   // replicate only: [warp][P 256 | Q 256]
+    double* const stage = sStage + warp * (2 * 32 * kScanItems);
     for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
         const uint32_t m = scan_tile_count(P, tile);
         // exclusive prefix of the tile: segment base (+) in-segment prefix
@@ -356,8 +362,11 @@ __global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_c
             const Run2 et = run2_combine(wpre, excl, double(kScanItems * lane));
             const Run2 full = run2_combine(tile_excl, et, double(k0));
             wpre = run2_combine(wpre, tot, double(32 * kScanItems));
-            const bool has_final = idx0 + kScanItems + 1 >= P.n && idx0 < P.n;   // P[n-1] / P[n-2] live here
-            if (k0 + kScanItems <= m && !has_final) {
+            // Warp-uniform: the whole pass (256 samples) lies inside the grid and holds
+            // neither P[n-1] nor P[n-2] (those go to the scalar block, slow path below).
+            const uint64_t pass0 = tile * uint64_t(kScanTile) + uint64_t(j) * (32 * kScanItems);
+            const bool pass_fast = uint32_t(j + 1) * (32 * kScanItems) <= m && pass0 + 32 * kScanItems + 1 < P.n;
+            if (pass_fast) {
                 // fast path: a full run of 8 samples, stored as 2 x 256 bits per table
                 double p = 0.0, q = 0.0;
 #pragma unroll
@@ -372,13 +381,30 @@ __global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_c
                     }
                     ptx::st_f64x4(st.P + idx0 + 4 * half, Ph[0], Ph[1], Ph[2], Ph[3]);
                     ptx::st_f64x4(st.Q + idx0 + 4 * half, Qh[0], Qh[1], Qh[2], Qh[3]);
-                    if (replicate) {
+                    if (replicate) {   // stage for the peer stores below
+                        double* sp = stage + lane * kScanItems + 4 * half;
+                        *reinterpret_cast<double4*>(sp) = make_double4(Ph[0], Ph[1], Ph[2], Ph[3]);
+                        *reinterpret_cast<double4*>(sp + 32 * kScanItems) = make_double4(Qh[0], Qh[1], Qh[2], Qh[3]);
+                    }
+                }
+                if (replicate) {
+                    // Fused all-gather: the pass goes to every peer's tables in stores that
+                    // are contiguous across the warp (1 KB per instruction).  Stores over
+                    // NVLink are not merged by an L2 on the way out, so the lane-strided
+                    // layout used for local HBM would leave as 32-byte packets.
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const int o = i * 128 + lane * 4;
+                        const double4 pv = *reinterpret_cast<const double4*>(stage + o);
+                        const double4 qv = *reinterpret_cast<const double4*>(stage + 32 * kScanItems + o);
                         for (int r = 0; r < P.world; ++r) {
                             if (r == P.rank) continue;
-                            ptx::st_f64x4(st.peerP[r] + idx0 + 4 * half, Ph[0], Ph[1], Ph[2], Ph[3]);
-                            ptx::st_f64x4(st.peerQ[r] + idx0 + 4 * half, Qh[0], Qh[1], Qh[2], Qh[3]);
+                            ptx::st_f64x4(st.peerP[r] + pass0 + o, pv.x, pv.y, pv.z, pv.w);
+                            ptx::st_f64x4(st.peerQ[r] + pass0 + o, qv.x, qv.y, qv.z, qv.w);
                         }
                     }
+                    __syncwarp();
                 }
                 if (st.samples) {
                     ptx::st_f64x4(st.samples + idx0, v[0], v[1], v[2], v[3]);
@@ -466,24 +492,26 @@ __global__ void __launch_bounds__(kScanThreads, MINB) scan_kernel(const __grid_c
     }
 }
 
-// Resident CTAs per SM the scan runs with.  2 by default (measured best on B200: 126
-// registers let the compiler overlap the passes of a tile; 3 and 4 CTAs trade that for
-// occupancy and lose); B200QUAD_SCAN_CTAS=2|3|4 overrides it for tuning runs.
-int scan_ctas_per_sm() {
-    static int v = [] {
-        const char* e = getenv("B200QUAD_SCAN_CTAS");
-        const int k = e ? atoi(e) : 0;
-        return (k >= 2 && k <= 4) ? k : 2;
-    }();
-    return v;
-}
-
-template <class F, int MINB>
-cudaError_t launch_scan_fm(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
+template <class F, bool REPL>
+cudaError_t launch_scan_fr(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(grid, 1, 1);
     lc.blockDim = dim3(kScanThreads, 1, 1);
     lc.stream = stream;
+    // staging for the coalesced peer stores of the fused all-gather
+    lc.dynamicSmemBytes = REPL ? kScanStageBytes : 0;
+    if (REPL) {
+        // static table + staging exceeds the default 48 KB for the table integrand: opt in once per device
+        static bool done[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !done[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(scan_kernel<F, REPL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 int(kScanStageBytes));
+            if (e != cudaSuccess) return e;
+            done[dev] = true;
+        }
+    }
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative;
     attr[0].val.cooperative = 1;
@@ -492,35 +520,30 @@ cudaError_t launch_scan_fm(const ScanPlan& P, const ScanState& st, unsigned grid
     ScanParams prm;
     prm.P = P;
     prm.st = st;
-    return cudaLaunchKernelEx(&lc, scan_kernel<F, MINB>, prm);
+    return cudaLaunchKernelEx(&lc, scan_kernel<F, REPL>, prm);
 }
 
 template <class F>
 cudaError_t launch_scan_f(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
-    switch (scan_ctas_per_sm()) {
-        case 4: return launch_scan_fm<F, 4>(P, st, grid, stream);
-        case 3: return launch_scan_fm<F, 3>(P, st, grid, stream);
-        default: return launch_scan_fm<F, 2>(P, st, grid, stream);
-    }
+    const bool replicate = P.world > 1 && (P.flags & kScanReplicate);
+    return replicate ? launch_scan_fr<F, true>(P, st, grid, stream) : launch_scan_fr<F, false>(P, st, grid, stream);
 }
 
-template <class F, int MINB>
-int occupancy_fm() {
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, scan_kernel<F, MINB>, kScanThreads, 0) != cudaSuccess) {
+// Co-resident CTAs per SM of both instantiations (the launch is cooperative).  The
+// replicate kernel's static + staging shared memory exceeds the default 48 KB for the
+// table integrand, so the opt-in has to precede the query or it reports zero.
+template <class F>
+int occupancy_f() {
+    int plain = 0, repl = 0;
+    cudaFuncSetAttribute(scan_kernel<F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kScanStageBytes));
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&plain, scan_kernel<F, false>, kScanThreads, 0) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&repl, scan_kernel<F, true>, kScanThreads, kScanStageBytes) !=
+            cudaSuccess) {
         cudaGetLastError();
         return 1;
     }
+    const int n = plain < repl ? plain : repl;
     return n < 1 ? 1 : n;
-}
-
-template <class F>
-int occupancy_f() {
-    switch (scan_ctas_per_sm()) {
-        case 4: return occupancy_fm<F, 4>();
-        case 3: return occupancy_fm<F, 3>();
-        default: return occupancy_fm<F, 2>();
-    }
 }
 
 }  // namespace
@@ -529,7 +552,7 @@ int scan_max_grid(int /*device*/, int sm_count) {
     int occ = occupancy_f<ProfileF>();
     const int o2 = occupancy_f<DisF>();
     if (o2 < occ) occ = o2;
-    if (occ > scan_ctas_per_sm()) occ = scan_ctas_per_sm();
+    if (occ > 2) occ = 2;
     return occ * sm_count;
 }
 

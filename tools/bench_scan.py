@@ -16,6 +16,7 @@ if os.path.exists("MEASURED_PEAKS.json"):
 hbm = float(peaks.get("hbm_gbs", 6551.4))
 
 ctx = parallel.context(0)
+sampler = bq.utils.ClockSampler(0, 2).start()
 dev = torch.device("cuda", 0)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 for name, n, dx in (("profile", 18_000_000, 1e-4), ("profile", 1 << 26, 1800.0 / (1 << 26)),
@@ -41,8 +42,9 @@ for name, n, dx in (("profile", 18_000_000, 1e-4), ("profile", 1 << 26, 1800.0 /
     gbs = 16.0 * n / (best * 1e-3) / 1e9
     print(json.dumps({"bench": "cumulative", "integrand": name, "n": n, "device_ms": round(best, 4),
                       "kernel_us": round(kbest, 1), "phase_end_us(A+prefix,bases,B)": phases,
-                      "scan_ctas_per_sm": int(os.environ.get("B200QUAD_SCAN_CTAS", "2")), "out_GBps": round(gbs, 1),
+ "out_GBps": round(gbs, 1),
                       "frac_of_hbm_copy_peak": round(gbs / hbm, 3),
                       "gsamples_per_s": round(n / best / 1e6, 2),
                       "p_last_dx": float(r.p_last) * dx}), flush=True)
     del P, Q
+print(json.dumps({"clocks": sampler.stop()}))
