@@ -35,7 +35,8 @@ class Result(C.Structure):
                 ("seg_lo", C.c_double * SEGMENTS), ("t_start_ns", C.c_uint64),
                 ("t_end_ns", C.c_uint64), ("n", C.c_uint64), ("status", C.c_int32),
                 ("eval_used", C.c_int32), ("world", C.c_int32), ("rank", C.c_int32),
-                ("device_ms", C.c_float), ("launches", C.c_int32), ("reserved", C.c_uint64 * 2)]
+                ("device_ms", C.c_float), ("launches", C.c_int32), ("seq", C.c_uint64),
+                ("reserved", C.c_uint64)]
 
 
 class ScanJob(C.Structure):
@@ -86,6 +87,7 @@ def _declare(lib, cuda):
     sig("bq_ctx_configure", i32, vp, i32, i32, i32)
     sig("bq_ctx_set_timeout_ms", i32, vp, i32)
     sig("bq_integrate", i32, vp, P(Job), P(Result))
+    sig("bq_integrate_value", i32, vp, P(Job), P(dbl), P(Result))
     sig("bq_integrate_async", i32, vp, P(Job), vp)
     sig("bq_result_fetch", i32, vp, P(Result))
     sig("bq_ctx_device_result", vp, vp)

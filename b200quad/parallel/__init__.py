@@ -55,6 +55,15 @@ class Context:
         check(rc, "bq_integrate")
         return res
 
+    def integrate_value(self, job):
+        """The integral as a float, lowest latency: one launch, no events, the host watches the
+        completion word the kernel writes last into the pinned result block."""
+        val = C.c_double()
+        rc = self.lib.bq_integrate_value(self.handle, C.byref(job), C.byref(val), None)
+        if rc:
+            check(rc, "bq_integrate_value")
+        return val.value
+
     def integrate_async(self, job, stream=None):
         check(self.lib.bq_integrate_async(self.handle, C.byref(job), C.c_void_p(stream or 0)),
               "bq_integrate_async")

@@ -16,10 +16,10 @@ value      device-timed: CUDA events around each step on the launching stream,
            is one kernel: its 152-byte job description rides down in the launch's
            parameter buffer and the kernel itself writes the 224-byte result
            block into pinned, mapped host memory (no copy-engine operation).
-e2e.value  the public API bq.integrate_result() called K times, wall clock per
-           call on the host: builds the job, launches (host -> device: the job in
-           the parameter buffer), waits, reads the result block the kernel wrote
-           to pinned host memory (device -> host).
+e2e.value  the public API bq.integrate() called K times, wall clock per call on
+           the host: builds the job, launches (host -> device: the job in the
+           parameter buffer), waits for the completion word, reads the float out
+           of the result block the kernel wrote to pinned host memory.
 """
 import argparse
 import json
@@ -158,18 +158,21 @@ def main():
     kern_ns = int(res.t_end_ns) - int(res.t_start_ns)
 
     # ---- end-to-end arm: the public API, one synchronous call per step --------
+    # bq.integrate() is the call a user makes: it returns the float the kernel wrote to host memory.
     for _ in range(args.warmup):
-        bq.integrate_result(args.integrand, a, b, n, args.rule, dtype=args.dtype, eval=args.eval)
+        bq.integrate(args.integrand, a, b, n, args.rule, dtype=args.dtype, eval=args.eval)
     barrier()
     e2e_s = 0.0
-    last = None
+    e2e_value_last = None
     for _ in range(args.steps):
         t0 = time.perf_counter()
-        last = bq.integrate_result(args.integrand, a, b, n, args.rule, dtype=args.dtype,
-                                   eval=args.eval)
+        e2e_value_last = bq.integrate(args.integrand, a, b, n, args.rule, dtype=args.dtype, eval=args.eval)
         e2e_s += time.perf_counter() - t0
         flush.zero_()
         torch.cuda.synchronize(dev)
+    barrier()
+    last = bq.integrate_result(args.integrand, a, b, n, args.rule, dtype=args.dtype, eval=args.eval)
+    assert last.value == e2e_value_last, (last.value, e2e_value_last)
     barrier()
 
     t = torch.tensor([dev_ms, e2e_s * 1e3, float(kern_ns)], dtype=torch.float64, device=dev)
@@ -200,8 +203,8 @@ def main():
                     "h2d_bytes_per_step": bytes_h2d(), "d2h_bytes_per_step": bytes_d2h(),
                     "h2d_path": "job description (sizeof Plan) in the kernel-launch parameter buffer; "
                                 "the workload has no input tensors",
-                    "d2h_path": "result block written by the kernel into pinned mapped host memory, "
-                                "read by the host after the stream synchronises"},
+                    "d2h_path": "result block written by the kernel into pinned mapped host memory; the host "
+                                "watches the block's completion word and reads the float from it"},
             "gpu_launches": args.steps * args.gpus,
             "gpu_launches_per_rank": args.steps,
             "kernel_us_last_step": kern_ns / 1e3,

@@ -241,6 +241,7 @@ static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint3
     st.ticket = c->d_ticket;
     st.result = c->d_result;
     st.result_host = c->h_result_dev;   // the kernel itself writes the result block to the host
+    st.seq = ++c->quad_seq;
     st.comm = c->d_comm;
     for (int r = 0; r < BQ_MAX_WORLD; ++r) st.peers[r] = c->peers[r];
     st.peers[rank] = c->d_comm;
@@ -295,6 +296,41 @@ int bq_integrate(bq_ctx* c, const bq_job* job, bq_result* out) {
     out->device_ms = ms;
     if (out->status != BQ_OK) set_error("kernel reported status %d", out->status);
     return out->status;
+}
+
+int bq_integrate_value(bq_ctx* c, const bq_job* job, double* value, bq_result* out) {
+    if (!c || !job) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    int rc = quad_enqueue(c, job, c->rank, c->world, 0, nullptr, c->stream);
+    if (rc != BQ_OK) return rc;
+    // The kernel writes the block's call number last (after a system fence): watch it
+    // instead of paying for a stream synchronise.  Every few thousand polls ask the
+    // driver, so a failed launch or a lost kernel cannot spin forever.
+    const uint64_t want = c->quad_seq;
+    const volatile uint64_t* flag = &c->h_result->seq;
+    for (uint32_t spins = 0; *flag != want; ++spins) {
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+        if ((spins & 0xfff) == 0xfff) {
+            const cudaError_t q = cudaStreamQuery(c->stream);
+            if (q == cudaSuccess) break;             // finished: the block is complete
+            if (q != cudaErrorNotReady) {
+                set_error("integrate kernel failed: %s", cudaGetErrorString(q));
+                return BQ_ERR_CUDA;
+            }
+        }
+    }
+    __atomic_thread_fence(__ATOMIC_ACQUIRE);
+    if (*flag != want) BQ_CUDA(cudaStreamSynchronize(c->stream));
+    const bq_result* r = c->h_result;
+    if (value) *value = r->value;
+    if (out) {
+        *out = *r;
+        out->device_ms = float(double(r->t_end_ns - r->t_start_ns) * 1e-6);   // kernel time (globaltimer)
+    }
+    if (r->status != BQ_OK) set_error("kernel reported status %d", r->status);
+    return r->status;
 }
 
 // ---- peers ---------------------------------------------------------------

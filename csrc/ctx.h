@@ -61,6 +61,7 @@ struct bq_ctx {
     bool peer_ipc[BQ_MAX_WORLD];
 
     uint64_t launches = 0;
+    uint64_t quad_seq = 0;                // call number of the latest integrate launch
 };
 
 namespace bq {

@@ -16,6 +16,7 @@
 // tcgen05/TMEM are not used; the one bulk transfer (the PROFILE table) goes
 // through a 1-D TMA copy (cp.async.bulk -> UBLKCP).
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdio.h>
 
 #include <type_traits>
@@ -488,17 +489,24 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
         if (status != BQ_OK) st.result->value = nan("");
         st.result->status = status;
         *st.ticket = 0u;
+        st.result->seq = st.seq;
         st.result->t_end_ns = ptx::globaltimer();
     }
     // The device -> host leg of the call: the result block goes straight into
     // the context's pinned, mapped host block (one 8-byte word per lane, a
     // single PCIe write burst) — no copy engine operation follows the kernel.
+    // The call number goes last, after a system-scope fence, so a host that
+    // watches that word sees a complete block.
     if (st.result_host) {
         __syncwarp();
         static_assert(sizeof(bq_result) % 8 == 0 && sizeof(bq_result) / 8 <= 32, "result block = one word per lane");
+        constexpr int kSeqWord = int(offsetof(bq_result, seq) / 8);
         const unsigned long long* src = reinterpret_cast<const unsigned long long*>(st.result);
-        unsigned long long* dst = reinterpret_cast<unsigned long long*>(st.result_host);
-        if (lane < int(sizeof(bq_result) / 8)) dst[lane] = src[lane];
+        volatile unsigned long long* dst = reinterpret_cast<volatile unsigned long long*>(st.result_host);
+        if (lane < int(sizeof(bq_result) / 8) && lane != kSeqWord) dst[lane] = src[lane];
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) dst[kSeqWord] = st.seq;
     }
 }
 

@@ -87,7 +87,9 @@ typedef struct bq_result {
     int32_t rank;
     float device_ms;           /* cudaEvent time of the launch (sync calls)   */
     int32_t launches;          /* kernels launched for this call (always 1)   */
-    uint64_t reserved[2];
+    uint64_t seq;              /* call number of the context; in the host copy of the block it is
+                                  the LAST word the kernel writes (completion flag)           */
+    uint64_t reserved;
 } bq_result;
 
 /* ---- cumulative integration (scan) -------------------------------------
@@ -148,8 +150,8 @@ int bq_cpu_cumulative(const bq_scan_job* job, int threads, double* P, double* Q,
 
 typedef struct bq_ctx bq_ctx;
 
-/* One context per (process, device).  Allocates: param block, partials,
- * ticket, result block, comm block (peer-visible), pinned staging ring. */
+/* One context per (process, device).  Allocates: partials, ticket, result
+ * blocks (device + pinned mapped host), comm block (peer-visible). */
 int bq_ctx_create(int device, bq_ctx** out);
 void bq_ctx_destroy(bq_ctx* ctx);
 int bq_ctx_device(const bq_ctx* ctx);
@@ -163,11 +165,17 @@ int bq_ctx_configure(bq_ctx* ctx, int ctas_per_sm, int cluster, int rows_per_til
 /* In-kernel barrier time-out in milliseconds (default 2000). */
 int bq_ctx_set_timeout_ms(bq_ctx* ctx, int ms);
 
-/* Synchronous: pinned params -> H2D -> one fused kernel -> D2H result. */
+/* Synchronous: ONE kernel launch (the job rides in the launch parameters, the
+ * kernel writes the result block into pinned host memory), bracketed by two
+ * events for out->device_ms. */
 int bq_integrate(bq_ctx* ctx, const bq_job* job, bq_result* out);
-/* Asynchronous on `stream` (cudaStream_t; NULL = ctx stream): enqueues the
- * H2D of the params, the kernel and the D2H of the result into pinned memory.
- * bq_result_fetch() synchronises and copies the result out. */
+/* Lowest-latency synchronous call: no events, and instead of a stream
+ * synchronise the host watches the completion word (bq_result.seq) the kernel
+ * writes last into the pinned result block.  out may be NULL; *value gets the
+ * integral.  This is what the Python integrate() calls. */
+int bq_integrate_value(bq_ctx* ctx, const bq_job* job, double* value, bq_result* out);
+/* Asynchronous on `stream` (cudaStream_t; NULL = ctx stream): enqueues the one
+ * kernel.  bq_result_fetch() synchronises and copies the result out. */
 int bq_integrate_async(bq_ctx* ctx, const bq_job* job, void* stream);
 int bq_result_fetch(bq_ctx* ctx, bq_result* out);
 /* Device pointer of the result block of the most recent launch. */

@@ -197,3 +197,28 @@ def test_peer_timeout_is_reported_not_hung():
         c.set_timeout_ms(2000)
     res = w.integrate(job)
     assert all(r.status == 0 for r in res)
+
+
+def test_value_fast_path_matches_and_survives_back_to_back_calls():
+    """bq.integrate() takes the event-free path (completion word in the pinned result block):
+    same bits as the event-timed call, and the word protocol holds over many calls in a row."""
+    ctx = parallel.context(0)
+    for n in (1, 1000, (1 << 20) + 3, 1 << 26):
+        for rule in RULES:
+            job = bq.make_job("sin", 0.0, math.pi, n, rule)
+            assert ctx.integrate_value(job) == ctx.integrate(job).value
+    ref = bq.integrate_result("sin", 0.1, 2.0, 12345, "mid", backend="cuda").value
+    for _ in range(2000):
+        assert bq.integrate("sin", 0.1, 2.0, 12345, "mid") == ref
+    big = bq.integrate_result("vel", 0.0, 1800.0, 1 << 24, backend="cuda").value
+    for _ in range(20):     # alternate sizes so a stale block would be noticed
+        assert bq.integrate("vel", 0.0, 1800.0, 1 << 24) == big
+        assert bq.integrate("sin", 0.1, 2.0, 12345, "mid") == ref
+
+
+def test_result_block_carries_call_number():
+    ctx = parallel.context(0)
+    job = bq.make_job("sin", 0.0, math.pi, 4096)
+    a = ctx.integrate(job).seq
+    b = ctx.integrate(job).seq
+    assert b == a + 1
