@@ -15,6 +15,7 @@
 
 #include "ctx.h"
 #include "host_common.h"
+#include "nvtx_range.h"
 #include "quad_launch.h"
 #include "scan_launch.h"
 
@@ -219,6 +220,7 @@ static LaunchConfig quad_config(const bq_ctx* c, const Plan& P) {
 
 static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint32_t extra_flags,
                         double* seg_out, cudaStream_t stream) {
+    NvtxRange range("b200quad::integrate");
     // The plan travels in the kernel parameter buffer: no staging copy.
     Plan plan;
     Plan* hp = &plan;

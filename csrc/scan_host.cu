@@ -6,6 +6,7 @@
 
 #include "ctx.h"
 #include "host_common.h"
+#include "nvtx_range.h"
 #include "scan_launch.h"
 
 namespace bq {
@@ -73,6 +74,7 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
         set_error("cumulative: output buffers must be 32-byte aligned");
         return BQ_ERR_INVALID;
     }
+    NvtxRange range("b200quad::cumulative");
     // The plan travels in the kernel parameter buffer: no staging copy.
     ScanPlan plan;
     ScanPlan* hp = &plan;
