@@ -218,8 +218,11 @@ static LaunchConfig quad_config(const bq_ctx* c, const Plan& P) {
     return cfg;
 }
 
+// to_host: the kernel also writes the result block into the pinned host block (the callers that
+// read it there); value_out: optional device address that receives the integral.
 static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint32_t extra_flags,
-                        double* seg_out, cudaStream_t stream) {
+                        double* seg_out, cudaStream_t stream, bool to_host = true,
+                        double* value_out = nullptr) {
     NvtxRange range("b200quad::integrate");
     // The plan travels in the kernel parameter buffer: no staging copy.
     Plan plan;
@@ -242,7 +245,8 @@ static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint3
     st.partials = c->d_partials;
     st.ticket = c->d_ticket;
     st.result = c->d_result;
-    st.result_host = c->h_result_dev;   // the kernel itself writes the result block to the host
+    st.result_host = to_host ? c->h_result_dev : nullptr;   // the kernel itself writes the block to the host
+    st.value_out = value_out;
     st.seq = ++c->quad_seq;
     st.comm = c->d_comm;
     for (int r = 0; r < BQ_MAX_WORLD; ++r) st.peers[r] = c->peers[r];
@@ -266,6 +270,13 @@ int bq_integrate_async(bq_ctx* c, const bq_job* job, void* stream) {
     DeviceGuard guard(c->device);
     cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
     return quad_enqueue(c, job, c->rank, c->world, 0, nullptr, s);
+}
+
+int bq_integrate_device_async(bq_ctx* c, const bq_job* job, double* d_value, void* stream) {
+    if (!c || !job || !d_value) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+    return quad_enqueue(c, job, c->rank, c->world, 0, nullptr, s, /*to_host=*/false, d_value);
 }
 
 int bq_integrate_local_async(bq_ctx* c, const bq_job* job, int rank, int world, double* dSegPairs,

@@ -27,6 +27,7 @@ struct DeviceState {
     unsigned int* ticket;     // clusters finished (reset by the last one)
     bq_result* result;        // device result block
     bq_result* result_host;   // pinned host result block as mapped on this device (or null)
+    double* value_out;        // optional: the integral also goes here (device memory, e.g. a tensor)
     uint64_t seq;             // call number: written last into the host block (completion word)
     CommBlock* comm;          // own comm block
     CommBlock* peers[BQ_MAX_WORLD];   // comm block of rank r as mapped here

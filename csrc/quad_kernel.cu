@@ -487,6 +487,7 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
         }
         finish_result<F>(P, f, hi, lo, st.result);
         if (status != BQ_OK) st.result->value = nan("");
+        if (st.value_out) *st.value_out = st.result->value;
         st.result->status = status;
         *st.ticket = 0u;
         st.result->seq = st.seq;

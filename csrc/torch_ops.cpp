@@ -3,8 +3,8 @@
 //   b200quad::integrate(int integrand, float a, float b, int n, int rule, int dtype,
 //                       int eval, int device) -> Tensor
 //       0-dim float64 tensor on `device` (CUDA index, or -1 for the CPU backend).
-//       Enqueued on torch's current CUDA stream: H2D of the parameters from the
-//       context's pinned ring, ONE fused kernel, result left on the device.
+//       Enqueued on torch's current CUDA stream: ONE fused kernel (the job rides in
+//       its launch parameters) that stores the integral into the output tensor.
 //   b200quad::cumulative(int integrand, float x0, float dx, int n, int device) -> (Tensor P, Tensor Q)
 //
 // The reference has no library surface at all (three main()s); this is the
@@ -62,12 +62,10 @@ at::Tensor integrate_op(int64_t integrand, double a, double b, int64_t n, int64_
     c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(device));
     bq_ctx* c = ctx_for(int(device));
     cudaStream_t stream = c10::cuda::getCurrentCUDAStream(static_cast<c10::DeviceIndex>(device));
-    const int rc = bq_integrate_async(c, &job, stream);
-    TORCH_CHECK(rc == BQ_OK, "b200quad: ", bq_last_error());
+    // ONE kernel: it stores the integral straight into the output tensor.
     at::Tensor out = at::empty({}, at::dtype(at::kDouble).device(at::kCUDA, device));
-    // bq_result.value is the first field of the device result block.
-    C10_CUDA_CHECK(cudaMemcpyAsync(out.data_ptr(), bq_ctx_device_result(c), sizeof(double),
-                                   cudaMemcpyDeviceToDevice, stream));
+    const int rc = bq_integrate_device_async(c, &job, out.data_ptr<double>(), stream);
+    TORCH_CHECK(rc == BQ_OK, "b200quad: ", bq_last_error());
     return out;
 }
 

@@ -178,6 +178,11 @@ int bq_integrate_value(bq_ctx* ctx, const bq_job* job, double* value, bq_result*
  * kernel.  bq_result_fetch() synchronises and copies the result out. */
 int bq_integrate_async(bq_ctx* ctx, const bq_job* job, void* stream);
 int bq_result_fetch(bq_ctx* ctx, bq_result* out);
+/* Device-resident variant (what the torch op calls): exactly one kernel, which
+ * stores the integral at d_value (device memory, 8-byte aligned) and the full
+ * block in the context's device result block; nothing is written to the host,
+ * so nothing at the end of the kernel waits for PCIe.  Capturable in a CUDA graph. */
+int bq_integrate_device_async(bq_ctx* ctx, const bq_job* job, double* d_value, void* stream);
 /* Device pointer of the result block of the most recent launch. */
 const bq_result* bq_ctx_device_result(const bq_ctx* ctx);
 
