@@ -90,6 +90,7 @@ def _declare(lib, cuda):
     sig("bq_integrate_value", i32, vp, P(Job), P(dbl), P(Result))
     sig("bq_integrate_async", i32, vp, P(Job), vp)
     sig("bq_integrate_device_async", i32, vp, P(Job), vp, vp)
+    sig("bq_device_result_fetch", i32, vp, P(Result))
     sig("bq_result_fetch", i32, vp, P(Result))
     sig("bq_ctx_device_result", vp, vp)
     sig("bq_cumulative", i32, vp, P(ScanJob), vp, vp, vp, P(ScanResult))

@@ -73,6 +73,16 @@ class Context:
         check(self.lib.bq_result_fetch(self.handle, C.byref(res)), "bq_result_fetch")
         return res
 
+    def integrate_device_async(self, job, d_value, stream=None):
+        """One kernel; the integral is stored at the device address d_value, nothing goes to the host."""
+        check(self.lib.bq_integrate_device_async(self.handle, C.byref(job), C.c_void_p(d_value),
+                                                 C.c_void_p(stream or 0)), "bq_integrate_device_async")
+
+    def fetch_device(self):
+        res = Result()
+        check(self.lib.bq_device_result_fetch(self.handle, C.byref(res)), "bq_device_result_fetch")
+        return res
+
     # -- cumulative -----------------------------------------------------------
     def cumulative(self, job, dP, dQ, dS=0):
         res = ScanResult()

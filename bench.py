@@ -14,8 +14,8 @@ over NVLink, result on every rank).
 value      device-timed: CUDA events around each step on the launching stream,
            L2 flushed between steps outside the events, max over ranks.  A step
            is one kernel: its 152-byte job description rides down in the launch's
-           parameter buffer and the kernel itself writes the 224-byte result
-           block into pinned, mapped host memory (no copy-engine operation).
+           parameter buffer; the result (every rank's copy) is left in device
+           memory, as in the NCCL comparator arm.
 e2e.value  the public API bq.integrate() called K times, wall clock per call on
            the host: builds the job, launches (host -> device: the job in the
            parameter buffer), waits for the completion word, reads the float out
@@ -134,11 +134,15 @@ def main():
         return bench_nccl_comparator(args, bq, ctx, job, n, dist, dev, stream, flush, rank, world, torch)
 
     # ---- device-timed arm ---------------------------------------------------
+    # The step's result stays in device memory here (a float64 tensor the kernel stores into),
+    # exactly like the NCCL comparator arm; delivering it to the host is what the e2e arm times.
+    d_value = torch.zeros(1, dtype=torch.float64, device=dev)
+    torch.cuda.synchronize(dev)
     for _ in range(args.warmup):
-        ctx.integrate_async(job)
+        ctx.integrate_device_async(job, d_value.data_ptr())
         with torch.cuda.stream(stream):
             flush.zero_()
-    res = ctx.fetch()
+    res = ctx.fetch_device()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
            for _ in range(args.steps)]
     sampler = bq.utils.ClockSampler(local_rank, 2).start() if rank == 0 else None
@@ -148,11 +152,12 @@ def main():
         with torch.cuda.stream(stream):
             flush.zero_()                      # L2 flush, outside the timed events
             e0.record(stream)
-        ctx.integrate_async(job)               # ONE kernel: params in, compute, combine, result to host
+        ctx.integrate_device_async(job, d_value.data_ptr())   # ONE kernel: params in, compute, combine
         e1.record(stream)
     barrier()
     wall1 = time.perf_counter()
-    res = ctx.fetch()
+    res = ctx.fetch_device()
+    device_arm_value = float(d_value)
     clocks = sampler.stop() if sampler else None
     dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in evs)
     kern_ns = int(res.t_end_ns) - int(res.t_start_ns)
@@ -172,7 +177,7 @@ def main():
         torch.cuda.synchronize(dev)
     barrier()
     last = bq.integrate_result(args.integrand, a, b, n, args.rule, dtype=args.dtype, eval=args.eval)
-    assert last.value == e2e_value_last, (last.value, e2e_value_last)
+    assert last.value == e2e_value_last == device_arm_value, (last.value, e2e_value_last, device_arm_value)
     barrier()
 
     t = torch.tensor([dev_ms, e2e_s * 1e3, float(kern_ns)], dtype=torch.float64, device=dev)

@@ -279,6 +279,14 @@ int bq_integrate_device_async(bq_ctx* c, const bq_job* job, double* d_value, voi
     return quad_enqueue(c, job, c->rank, c->world, 0, nullptr, s, /*to_host=*/false, d_value);
 }
 
+int bq_device_result_fetch(bq_ctx* c, bq_result* out) {
+    if (!c || !out) return BQ_ERR_INVALID;
+    DeviceGuard guard(c->device);
+    BQ_CUDA(cudaStreamSynchronize(c->last_stream ? c->last_stream : c->stream));
+    BQ_CUDA(cudaMemcpy(out, c->d_result, sizeof(bq_result), cudaMemcpyDeviceToHost));
+    return out->status;
+}
+
 int bq_integrate_local_async(bq_ctx* c, const bq_job* job, int rank, int world, double* dSegPairs,
                              void* stream) {
     if (!c || !job) return BQ_ERR_INVALID;

@@ -28,10 +28,12 @@ void set_error(const char* fmt, ...) {
 }
 const char* last_error() { return g_err; }
 
-// n below which AUTO stays with DIRECT evaluation: the ROTATE set-up (four
-// sincos per thread plus one per row) only pays off once a part has several
-// rows.  A function of n alone, so results do not depend on the world size.
-static constexpr uint64_t kRotateMinN = 1ull << 23;
+// n below which AUTO stays with DIRECT evaluation: the ROTATE set-up (three
+// sincos per thread plus one per 32 tiles) has to be paid back.  Measured on B200
+// (profiles/v6/sweep_n_v6.jsonl, device us DIRECT / ROTATE): 2^18 14.9 / 15.3,
+// 2^20 19.1 / 17.2, 2^22 27.8 / 21.4, 2^24 62 / 25.  A function of n alone, so
+// results do not depend on the world size.
+static constexpr uint64_t kRotateMinN = 1ull << 20;
 
 int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, int table_len,
               Plan* P) {

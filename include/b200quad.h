@@ -183,6 +183,8 @@ int bq_result_fetch(bq_ctx* ctx, bq_result* out);
  * block in the context's device result block; nothing is written to the host,
  * so nothing at the end of the kernel waits for PCIe.  Capturable in a CUDA graph. */
 int bq_integrate_device_async(bq_ctx* ctx, const bq_job* job, double* d_value, void* stream);
+/* Synchronises and copies the DEVICE result block of the most recent launch out. */
+int bq_device_result_fetch(bq_ctx* ctx, bq_result* out);
 /* Device pointer of the result block of the most recent launch. */
 const bq_result* bq_ctx_device_result(const bq_ctx* ctx);
 
