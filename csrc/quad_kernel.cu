@@ -236,9 +236,7 @@ struct PartWorker {
     // the tile loop has no CTA-wide barrier, and a flush group of full tiles
     // runs as one loop: one warp-level sync and one compensated flush per
     // kFlushTiles tiles.
-    __device__ __forceinline__ dd run(uint32_t part) const {
-        uint64_t lo64, hi64;
-        part_tiles(P, part, lo64, hi64);
+    __device__ __forceinline__ dd run(uint64_t lo64, uint64_t hi64) const {   // tiles [lo64, hi64) of a part
         dd total{0.0, 0.0};
         TileAcc<R> acc;
         acc.clear();
@@ -306,8 +304,10 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     double* const sX0 = reinterpret_cast<double*>(sDyn + sizeof(Vec2<R>) * (kThreads / 32) * 2 * Worker::kBufStride);
     __shared__ dd sWarpTot[kBatchSlots][kThreads / 32];   // per-warp part totals, reduced once per batch
     __shared__ dd sMine[kBatchSlots];                      // this CTA's part sums of the batch
+    __shared__ uint32_t sLo[kBatchSlots], sHi[kBatchSlots];   // tile range of each slot's part
     __shared__ __align__(16) dd sMail[kBatchChunks];       // DSMEM mailbox (leader CTA)
     __shared__ dd sSeg[kSegments];
+    __shared__ __align__(8) bq_result sRes;                // result block, assembled by lane 0 of the last warp
     __shared__ int sIsLast;
     constexpr bool kIsProfile = std::is_same<F, ProfileF>::value;
     __shared__ __align__(16) double sTable[kIsProfile ? kMaxTable : 2];
@@ -356,16 +356,23 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     const uint32_t pp = (csize == 2) ? 1u : uint32_t(kPartsPerChunk);   // parts per chunk done here
     for (uint32_t b_lo = my_lo; b_lo < my_hi; b_lo += kBatchChunks) {
         const uint32_t nb = my_hi - b_lo < uint32_t(kBatchChunks) ? my_hi - b_lo : uint32_t(kBatchChunks);
-        for (uint32_t k = 0; k < nb; ++k) {
-            for (uint32_t q = 0; q < pp; ++q) {
-                const uint32_t part = (b_lo + k) * kPartsPerChunk + (csize == 2 ? crank : q);
-                uint64_t lo, hi;
-                part_tiles(P, part, lo, hi);
-                trace_tiles += hi - lo;
-                dd t{0.0, 0.0};
-                if (lo < hi) t = warp_reduce_lazy(worker.run(part));   // small n: most parts hold no tile
-                if (lane == 0) sWarpTot[k * pp + q][warp] = t;
-            }
+        // Tile ranges of the batch's parts: one thread per slot works them out (two 64-bit
+        // divisions each) instead of every thread of the CTA repeating all of them — for small
+        // n, where most parts are empty, that repetition was most of a CTA's life.
+        if (uint32_t(tid) < nb * pp) {
+            const uint32_t k = uint32_t(tid) / pp, q = uint32_t(tid) % pp;
+            const uint32_t part = (b_lo + k) * kPartsPerChunk + (csize == 2 ? crank : q);
+            uint64_t lo, hi;
+            part_tiles(P, part, lo, hi);
+            sLo[tid] = uint32_t(lo), sHi[tid] = uint32_t(hi);   // n_tiles < 2^31
+        }
+        __syncthreads();
+        for (uint32_t slot = 0; slot < nb * pp; ++slot) {
+            const uint32_t lo = sLo[slot], hi = sHi[slot];
+            trace_tiles += hi - lo;
+            dd t{0.0, 0.0};
+            if (lo < hi) t = warp_reduce_lazy(worker.run(lo, hi));   // small n: most parts hold no tile
+            if (lane == 0) sWarpTot[slot][warp] = t;
         }
         __syncthreads();
         // Part sums: warp w finishes slots w, w + 8 (the 8-lane butterfly + one
@@ -416,6 +423,9 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     __syncthreads();
     if (!sIsLast) return;
     __threadfence();
+    // kernel-entry stamp of CTA 0 (ordered before this point by the ticket chain): fetched now so
+    // that the load is long done when the block is assembled
+    const uint64_t t_start = *reinterpret_cast<volatile const uint64_t*>(&st.result->t_start_ns);
 
     // ---- segment sums: one warp per owned segment, fixed order ---------------
     if (tid < kSegments) sSeg[tid] = dd{0.0, 0.0};
@@ -479,32 +489,38 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
         if (lane == 0) st.comm->epoch = epoch + 1;
     }
 
+    // The result block is assembled in shared memory and leaves in two warp-wide bursts (device
+    // block, host block): no thread reads back what another one just stored to global memory.
     if (lane == 0) {
         double hi[kSegments], lo[kSegments];
         for (int s = 0; s < kSegments; ++s) hi[s] = sSeg[s].hi, lo[s] = sSeg[s].lo;
         if (st.seg_out) {
             for (int s = 0; s < kSegments; ++s) st.seg_out[2 * s] = hi[s], st.seg_out[2 * s + 1] = lo[s];
         }
-        finish_result<F>(P, f, hi, lo, st.result);
-        if (status != BQ_OK) st.result->value = nan("");
-        if (st.value_out) *st.value_out = st.result->value;
-        st.result->status = status;
+        finish_result<F>(P, f, hi, lo, &sRes);
+        if (status != BQ_OK) sRes.value = nan("");
+        if (st.value_out) *st.value_out = sRes.value;
+        sRes.t_start_ns = t_start;
+        sRes.status = status;
+        sRes.device_ms = 0.f;
+        sRes.seq = st.seq;
+        sRes.reserved = 0;
         *st.ticket = 0u;
-        st.result->seq = st.seq;
-        st.result->t_end_ns = ptx::globaltimer();
+        sRes.t_end_ns = ptx::globaltimer();
     }
-    // The device -> host leg of the call: the result block goes straight into
-    // the context's pinned, mapped host block (one 8-byte word per lane, a
-    // single PCIe write burst) — no copy engine operation follows the kernel.
-    // The call number goes last, after a system-scope fence, so a host that
-    // watches that word sees a complete block.
+    __syncwarp();
+    static_assert(sizeof(bq_result) % 8 == 0 && sizeof(bq_result) / 8 <= 32, "result block = one word per lane");
+    constexpr int kWords = int(sizeof(bq_result) / 8);
+    constexpr int kSeqWord = int(offsetof(bq_result, seq) / 8);
+    const unsigned long long word = lane < kWords ? reinterpret_cast<const unsigned long long*>(&sRes)[lane] : 0ull;
+    if (lane < kWords) reinterpret_cast<unsigned long long*>(st.result)[lane] = word;
+    // The device -> host leg of the call: the block goes straight into the context's pinned,
+    // mapped host block (a single PCIe write burst) — no copy engine operation follows the
+    // kernel.  The call number goes last, after a system-scope fence, so a host that watches
+    // that word sees a complete block.
     if (st.result_host) {
-        __syncwarp();
-        static_assert(sizeof(bq_result) % 8 == 0 && sizeof(bq_result) / 8 <= 32, "result block = one word per lane");
-        constexpr int kSeqWord = int(offsetof(bq_result, seq) / 8);
-        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(st.result);
         volatile unsigned long long* dst = reinterpret_cast<volatile unsigned long long*>(st.result_host);
-        if (lane < int(sizeof(bq_result) / 8) && lane != kSeqWord) dst[lane] = src[lane];
+        if (lane < kWords && lane != kSeqWord) dst[lane] = word;
         __threadfence_system();
         __syncwarp();
         if (lane == 0) dst[kSeqWord] = st.seq;
