@@ -14,7 +14,7 @@ SEGMENTS = 8
 MAX_WORLD = 8
 IPC_HANDLE_BYTES = 64
 
-INTEGRANDS = {"sin": 0, "acc": 1, "vel": 2, "dis": 3, "profile": 4}
+INTEGRANDS = {"sin": 0, "acc": 1, "vel": 2, "dis": 3, "profile": 4, "custom": 5}
 RULES = {"left": 0, "right": 1, "mid": 2, "midpoint": 2, "trap": 3, "trapezoid": 3}
 DTYPES = {"fp64": 0, "f64": 0, "float64": 0, "fp32": 1, "f32": 1, "fp32c": 1, "float32": 1}
 EVALS = {"auto": 0, "direct": 1, "rotate": 2}
@@ -72,6 +72,7 @@ def _declare(lib, cuda):
     sig("bq_default_profile", P(dbl), P(i32))
     sig("bq_oracle_sin_sum", dbl, dbl, dbl, u64, i32)
     sig("bq_sizeof_params", C.c_size_t)
+    sig("bq_set_custom_integrand", i32, vp, vp)
     sig("bq_cpu_integrate", i32, P(Job), i32, P(Result))
     sig("bq_cpu_integrate_segments", i32, P(Job), i32, i32, i32, P(Result))
     sig("bq_fold_segments", i32, P(Job), P(dbl), P(dbl), P(Result))

@@ -122,3 +122,28 @@ def get(f):
 
 def names():
     return sorted(REGISTRY)
+
+
+def custom(expr, params=(0.0, 0.0, 0.0, 0.0), name=None):
+    """An integrand from a C++ expression in `x` and `p0..p3`, compiled into the fused kernel
+    (see models/jit.py).  The build happens on first use and is cached on disk."""
+    from . import jit as _custom
+    expr = str(expr).strip()
+    integ = Integrand(name or "custom:" + expr, _native.INTEGRANDS["custom"], params,
+                      doc="custom integrand: " + expr)
+    integ.expr = expr
+    ev = None
+
+    def fn(x):
+        # slow path / oracles: element-wise through the compiled host evaluator
+        nonlocal ev
+        if ev is None:
+            ev = _custom.evaluator(expr, integ.params)
+        xp = _xp(x)
+        if xp.__name__ == "torch":
+            flat = [ev(v) for v in x.detach().cpu().double().reshape(-1).tolist()]
+            return xp.tensor(flat, dtype=x.dtype, device=x.device).reshape(x.shape)
+        import numpy as np
+        return np.vectorize(ev)(np.asarray(x, dtype=np.float64))
+    integ.fn = fn
+    return integ

@@ -57,6 +57,11 @@ def make_job(f, a, b, n, rule="left", dtype="fp64", eval="auto", params=None):
     integ, _ = models.get(f)
     if integ is None:
         raise TypeError("make_job needs a library integrand")
+    if integ.native_id == _native.INTEGRANDS["custom"]:
+        from ..models import jit as _custom
+        _custom.activate(integ.expr)        # builds / loads its kernel on first use
+        if params is None:
+            params = integ.params
     try:
         job = Job(integ.native_id, _native.RULES[rule], _native.DTYPES[dtype], _native.EVALS[eval],
                   float(a), float(b), int(n), (C.c_double * 4)(*(params or (0.0, 0.0, 0.0, 0.0))))

@@ -23,6 +23,10 @@ int make_scan_plan(const bq_scan_job& job, int rank, int world, int table_len, S
         set_error("world=%d rank=%d: world must be 1, 2, 4 or 8", world, rank);
         return BQ_ERR_INVALID;
     }
+    if (job.integrand == BQ_F_CUSTOM) {
+        set_error("cumulative: custom integrands are supported by integrate() only");
+        return BQ_ERR_UNSUPPORTED;
+    }
     if (job.integrand < 0 || job.integrand >= BQ_F_COUNT || !isfinite(job.x0) || !isfinite(job.dx)) {
         set_error("cumulative: bad integrand / grid");
         return BQ_ERR_INVALID;

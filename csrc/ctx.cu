@@ -292,7 +292,7 @@ int bq_integrate_local_async(bq_ctx* c, const bq_job* job, int rank, int world, 
     if (!c || !job) return BQ_ERR_INVALID;
     DeviceGuard guard(c->device);
     cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
-    return quad_enqueue(c, job, rank, world, kFlagLocalOnly, dSegPairs, s);
+    return quad_enqueue(c, job, rank, world, kFlagLocalOnly, dSegPairs, s, /*to_host=*/false);
 }
 
 int bq_result_fetch(bq_ctx* c, bq_result* out) {

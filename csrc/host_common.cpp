@@ -28,6 +28,12 @@ void set_error(const char* fmt, ...) {
 }
 const char* last_error() { return g_err; }
 
+static bq_custom_launch_fn g_custom_launch = nullptr;
+static bq_custom_eval_fn g_custom_eval = nullptr;
+bq_custom_launch_fn custom_launch() { return g_custom_launch; }
+bq_custom_eval_fn custom_eval() { return g_custom_eval; }
+void set_custom(bq_custom_launch_fn l, bq_custom_eval_fn e) { g_custom_launch = l, g_custom_eval = e; }
+
 // n below which AUTO stays with DIRECT evaluation: the ROTATE set-up (three
 // sincos per thread plus one per 32 tiles) has to be paid back.  Measured on B200
 // (profiles/v6/sweep_n_v6.jsonl, device us DIRECT / ROTATE): 2^18 14.9 / 15.3,
@@ -69,7 +75,12 @@ int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, in
     P->rule = job.rule;
     P->dtype = job.dtype;
     for (int i = 0; i < 4; ++i) P->p[i] = job.p[i];
-    const bool trig = job.integrand != BQ_F_PROFILE;
+    const bool trig = job.integrand == BQ_F_SIN || job.integrand == BQ_F_ACC || job.integrand == BQ_F_VEL ||
+                      job.integrand == BQ_F_DIS;
+    if (job.integrand == BQ_F_CUSTOM && !custom_eval() && !custom_launch()) {
+        set_error("integrand BQ_F_CUSTOM but no custom integrand is registered (bq_set_custom_integrand)");
+        return BQ_ERR_INVALID;
+    }
     if (job.integrand == BQ_F_ACC || job.integrand == BQ_F_VEL || job.integrand == BQ_F_DIS) {
         if (P->p[0] == 0.0) P->p[0] = kTscale;
         if (P->p[1] == 0.0) P->p[1] = kAscale;
@@ -140,6 +151,10 @@ long double oracle_sin_sum(double a, double b, uint64_t n, int rule) {
 extern "C" {
 
 const char* bq_version(void) { return "b200quad 0.1 (sm_100a)"; }
+int bq_set_custom_integrand(bq_custom_launch_fn launch, bq_custom_eval_fn eval) {
+    bq::set_custom(launch, eval);
+    return BQ_OK;
+}
 const char* bq_last_error(void) { return bq::last_error(); }
 const double* bq_default_profile(int* len) { return bq::default_profile(len); }
 size_t bq_sizeof_params(void) { return sizeof(bq::Plan); }

@@ -94,4 +94,18 @@ struct ProfileF {
     BQ_HD R eval_sc(R x, R, R) const { return eval(x); }
 };
 
+// Host-side stand-in for a custom integrand (BQ_F_CUSTOM): calls the eval entry point of the
+// user's translation unit.  The GPU side never sees this type — there the expression itself is
+// compiled into the kernel (b200quad/models/jit.py generates that unit).
+struct CustomHostF {
+    static constexpr bool kTrig = false, kNeedS = false, kNeedC = false, kNeedX = true;
+    double (*fn)(double, const double*);
+    double p[4];
+    template <class R>
+    BQ_HD R eval(R x) const { return R(fn(double(x), p)); }
+    BQ_HD double angle(double) const { return 0.0; }
+    template <class R>
+    BQ_HD R eval_sc(R x, R, R) const { return eval(x); }
+};
+
 }  // namespace bq

@@ -1,0 +1,576 @@
+// The fused definite-integral kernel: ONE launch per GPU per integrate() call.
+//
+//   evaluate f on this rank's share of the n sample points        (hot loop,
+//      no CTA-wide or cluster-wide synchronisation inside it)
+//   -> per-thread dd totals -> warp shuffle -> per-warp part totals in smem
+//   -> once per CTA: cross-warp combine, then the thread-block cluster pair
+//      exchanges its part sums through DSMEM                       (chunk sums)
+//   -> ticket; the last cluster folds chunk sums into segment sums
+//   -> publish segment pairs into every peer's comm block over NVLink,
+//      in-kernel epoch barrier, fixed-order fold, *h, rule epilogue -> result
+//
+// Replaces, in the reference: the per-thread loops + host sum of
+// cintegrate.cu:47-98,135-138; riemann_sum + MPI_Send/Recv gather of
+// riemann.cpp:29-44,76,82-85; MPI_Reduce/MPI_Barrier of 4main.c:134,137,200.
+// No tensor-core work exists in this workload (no matrix product), so
+// tcgen05/TMEM are not used; the one bulk transfer (the PROFILE table) goes
+// through a 1-D TMA copy (cp.async.bulk -> UBLKCP).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdio.h>
+
+#include <type_traits>
+
+#include "device_state.h"
+#include "ptx.cuh"
+#include "quad_core.cuh"
+#include "quad_launch.h"
+
+// Rows of the ROTATE loop unrolled together.  Measured on B200 at n = 2^32 (fp64 / fp32,
+// G intervals/s): 2: 5458 / 8281, 4: 5528 / 8660, 8: 5645 / 8684, 16: 5702 / 8616.
+#ifndef BQ_ROT_UNROLL
+#define BQ_ROT_UNROLL 16
+#endif
+#ifndef BQ_ROT_UNROLL_F32
+#define BQ_ROT_UNROLL_F32 8
+#endif
+#ifndef BQ_MIN_CTAS
+#define BQ_MIN_CTAS 2
+#endif
+
+namespace bq {
+
+template <class R>
+struct RotUnroll {
+    static constexpr int value = sizeof(R) == 8 ? BQ_ROT_UNROLL : BQ_ROT_UNROLL_F32;
+};
+
+template <class R>
+struct Vec2;
+template <>
+struct __align__(16) Vec2<double> {
+    double x, y;
+};
+template <>
+struct __align__(8) Vec2<float> {
+    float x, y;
+};
+
+__device__ __forceinline__ dd shfl_xor_dd(dd v, int off) {
+    return dd{__shfl_xor_sync(0xffffffffu, v.hi, off), __shfl_xor_sync(0xffffffffu, v.lo, off)};
+}
+
+// Butterfly over the 32 lanes; every lane ends with the same pair.
+__device__ __forceinline__ dd warp_reduce_dd(dd v) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v = dd_add(v, shfl_xor_dd(v, off));
+    return v;
+}
+// Same shape with un-normalised pairs (shorter dependent chain); see bq_dd.cuh.
+__device__ __forceinline__ dd warp_reduce_lazy(dd v) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v = dd_add_lazy(v, shfl_xor_dd(v, off));
+    return v;
+}
+
+template <class F, class R, int MODE>
+struct PartWorker {
+    static constexpr bool kRotate = (MODE == BQ_EVAL_ROTATE);
+
+    const Plan& P;        // kernel parameter (constant bank)
+    const F& f;
+    Vec2<R>* wSC;         // this warp's private row bases: [2][kBufStride]
+    double* wX0;          // this warp's private row x0:    [2][kBufStride] (integrands that need x)
+    const double h, a;    // register copies for the hot loops
+    const uint32_t rows;  // rows of every tile but the last
+    const uint64_t last_tile, tile_pts;
+    // column constants
+    R cj[kCols], sj[kCols];
+    double dx[kCols];     // ROTATE: x offset of the column; DIRECT: column index as double
+    SinCos rowrot;        // ROTATE: rotation of row `lane` relative to the tile base
+
+    __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R>* sc, double* x0)
+        : P(P_), f(f_), wSC(sc), wX0(x0), h(P_.h), a(P_.a), rows(P_.rows),
+          last_tile(P_.n_tiles - 1), tile_pts(P_.tile_pts) {
+        const int lane = threadIdx.x & 31;
+        if (kRotate) {
+            // Two sincos per thread for all kCols columns: the thread's own
+            // offset, and (lane & 7)'s block offset shared through shuffles.
+            SinCos mine, blk;
+            sincos(f.angle(double(threadIdx.x) * h), &mine.s, &mine.c);
+            sincos(f.angle(double((lane & (kCols - 1)) * kThreads) * h), &blk.s, &blk.c);
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) {
+                SinCos bj;
+                bj.s = __shfl_sync(0xffffffffu, blk.s, j);
+                bj.c = __shfl_sync(0xffffffffu, blk.c, j);
+                const SinCos cs = rotate_sc(mine, bj);
+                cj[j] = R(cs.c);
+                sj[j] = R(cs.s);
+                dx[j] = double(threadIdx.x + kThreads * j) * h;
+            }
+            sincos(f.angle(double(lane) * double(kWidth) * h), &rowrot.s, &rowrot.c);
+        } else {
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) {
+                dx[j] = double(threadIdx.x + kThreads * j);
+                cj[j] = R(0);
+                sj[j] = R(0);
+            }
+            rowrot = SinCos{0.0, 1.0};
+        }
+    }
+
+    // Accurate sincos of the base angle of tile `first + lane` (one pass serves 32 tiles).
+    __device__ __forceinline__ SinCos group_bases(uint64_t first, uint64_t hi) const {
+        const uint64_t tile = first + (threadIdx.x & 31);
+        SinCos g{0.0, 1.0};
+        if (tile < hi) {
+            const double xt = fma(double(tile * tile_pts) + P.off, h, a);
+            sincos(f.angle(xt), &g.s, &g.c);
+        }
+        return g;
+    }
+
+    // Rows of a flush group: kFlushTiles tiles x kMaxRows rows.  The row bases of a
+    // whole group sit contiguously in this warp's buffer, so a group of full
+    // tiles is one software-pipelined loop of kGroupRows rows.
+    static constexpr int kGroupRows = kFlushTiles * kMaxRows;
+    static constexpr int kBufStride = kGroupRows + 2;   // +1 prefetch slot, kept even
+
+    // Row bases of the group of `nt` tiles starting at tile t0: for each tile,
+    // lane r rotates the tile base by r rows (4 fp64 ops) and parks the pair in
+    // this warp's private buffer.  `grp` carries the accurate tile bases of the
+    // current run of 32 tiles (refreshed here when t0 starts a new run).
+    __device__ __forceinline__ void group_row_bases(uint32_t t0, uint32_t nt, uint32_t lo, uint32_t hi,
+                                                    SinCos& grp, int buf) const {
+        const int lane = threadIdx.x & 31;
+        if (((t0 - lo) & 31u) == 0u) grp = group_bases(t0, hi);
+        Vec2<R>* sc = wSC + buf * kBufStride + lane;
+        double* x0 = wX0 + buf * kBufStride + lane;
+#pragma unroll
+        for (uint32_t k = 0; k < uint32_t(kFlushTiles); ++k) {
+            if (k < nt) {
+                const int src = int((t0 + k - lo) & 31u);
+                const SinCos tb{__shfl_sync(0xffffffffu, grp.s, src), __shfl_sync(0xffffffffu, grp.c, src)};
+                const SinCos rb = rotate_sc(tb, rowrot);
+                sc[k * kMaxRows] = Vec2<R>{R(rb.s), R(rb.c)};
+                if (F::kNeedX)
+                    x0[k * kMaxRows] =
+                        fma(double(uint64_t(t0 + k) * tile_pts + uint64_t(lane) * kWidth) + P.off, h, a);
+            }
+        }
+    }
+
+    // `nrows` full rows starting at row-base slot 0 of sc_row / x0_row.
+    // Software-pipelined: the next row's base is in flight while this row's
+    // 24 fp64 instructions issue (slot nrows is valid memory).
+    template <class Count>
+    __device__ __forceinline__ void rows_rotate(const Vec2<R>* sc_row, const double* x0_row, Count nrows,
+                                                TileAcc<R>& acc, Vec2<R>& sc, double& x0) const {
+        sc = sc_row[0];
+        x0 = F::kNeedX ? x0_row[0] : 0.0;
+        constexpr int kUnroll = RotUnroll<R>::value;
+#pragma unroll kUnroll
+        for (Count r = 0; r < nrows; ++r) {
+            const Vec2<R> sc_next = sc_row[r + 1];
+            const double x0_next = F::kNeedX ? x0_row[r + 1] : 0.0;
+            R v[kCols];
+#pragma unroll
+            for (int j = 0; j < kCols; ++j)
+                v[j] = point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]);
+            acc.add_row(v);
+            sc = sc_next;
+            x0 = x0_next;
+        }
+    }
+
+    // ROTATE, any tile (short last tile, tiles of fewer than kMaxRows rows).
+    __device__ __forceinline__ void tile_rotate(uint32_t tile, const Vec2<R>* sc_row, const double* x0_row,
+                                                TileAcc<R>& acc) const {
+        uint32_t full_rows = rows, rem = 0;
+        if (tile == last_tile) {
+            const TileGeom g = tile_geom(P, tile);
+            full_rows = g.full_rows, rem = g.rem;
+        }
+        Vec2<R> sc;
+        double x0;
+        rows_rotate<uint32_t>(sc_row, x0_row, full_rows, acc, sc, x0);
+        if (rem) {   // sc / x0 already hold row full_rows
+#pragma unroll
+            for (int j = 0; j < kCols; ++j)
+                if (threadIdx.x + kThreads * j < rem)
+                    acc.add_one(j, point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]));
+        }
+    }
+
+    // DIRECT: adds every sample of `tile` into `acc`.  Only the globally last tile can be short.
+    __device__ __forceinline__ void tile_direct(uint64_t tile, TileAcc<R>& acc) const {
+        TileGeom g;
+        if (tile == last_tile) {
+            g = tile_geom(P, tile);
+        } else {
+            g.start = tile * tile_pts;
+            g.full_rows = rows;
+            g.rem = 0;
+        }
+        double rb = row_base_index(P, g, 0);
+#pragma unroll 2
+        for (uint32_t r = 0; r < g.full_rows; ++r) {
+            R v[kCols];
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) v[j] = point_direct<F, R>(f, rb, dx[j], h, a);
+            acc.add_row(v);
+            rb += double(kWidth);
+        }
+        if (g.rem) {
+#pragma unroll
+            for (int j = 0; j < kCols; ++j)
+                if (threadIdx.x + kThreads * j < g.rem)
+                    acc.add_one(j, point_direct<F, R>(f, rb, dx[j], h, a));
+        }
+    }
+
+    // All tiles of one part; returns this thread's dd total.  In ROTATE mode a
+    // warp is self-sufficient (its own bases, its own shared-memory buffer), so
+    // the tile loop has no CTA-wide barrier, and a flush group of full tiles
+    // runs as one loop: one warp-level sync and one compensated flush per
+    // kFlushTiles tiles.
+    __device__ __forceinline__ dd run(uint64_t lo64, uint64_t hi64) const {   // tiles [lo64, hi64) of a part
+        dd total{0.0, 0.0};
+        TileAcc<R> acc;
+        acc.clear();
+        if (kRotate) {
+            const uint32_t lo = uint32_t(lo64), hi = uint32_t(hi64);   // n_tiles < 2^31
+            if (lo >= hi) return total;
+            const uint32_t last = uint32_t(last_tile);
+            SinCos grp{0.0, 1.0};
+            int buf = 0;
+            group_row_bases(lo, hi - lo < uint32_t(kFlushTiles) ? hi - lo : uint32_t(kFlushTiles), lo, hi, grp, 0);
+            __syncwarp();
+            for (uint32_t t = lo; t < hi; t += kFlushTiles) {
+                const uint32_t nt = hi - t < uint32_t(kFlushTiles) ? hi - t : uint32_t(kFlushTiles);
+                if (t + kFlushTiles < hi) {
+                    const uint32_t left = hi - t - kFlushTiles;
+                    group_row_bases(t + kFlushTiles, left < uint32_t(kFlushTiles) ? left : uint32_t(kFlushTiles),
+                                    lo, hi, grp, buf ^ 1);
+                }
+                const Vec2<R>* sc_row = wSC + buf * kBufStride;
+                const double* x0_row = wX0 + buf * kBufStride;
+                if (nt == uint32_t(kFlushTiles) && rows == uint32_t(kMaxRows) && t + kFlushTiles - 1 < last) {
+                    Vec2<R> sc;
+                    double x0;
+                    rows_rotate<int>(sc_row, x0_row, kGroupRows, acc, sc, x0);
+                } else {
+                    for (uint32_t k = 0; k < nt; ++k)
+                        tile_rotate(t + k, sc_row + k * kMaxRows, x0_row + k * kMaxRows, acc);
+                }
+                total = dd_acc_lazy(total, acc.flush());
+                acc.clear();
+                __syncwarp();
+                buf ^= 1;
+            }
+        } else {
+            for (uint64_t t = lo64; t < hi64; ++t) {
+                tile_direct(t, acc);
+                if (((t - lo64) & (kFlushTiles - 1)) == kFlushTiles - 1 || t + 1 == hi64) {
+                    total = dd_acc_lazy(total, acc.flush());
+                    acc.clear();
+                }
+            }
+        }
+        return total;   // un-normalised; renormalised once per part after the cross-warp combine
+    }
+};
+
+// Parts a CTA reduces in one go: its share of up to kBatchChunks chunks
+// (one part per chunk when a cluster pair splits the chunk, else both).
+constexpr int kBatchChunks = 8;
+constexpr int kBatchSlots = kBatchChunks * kPartsPerChunk;
+
+struct QuadParams {
+    Plan P;            // 152 bytes, rides in the kernel parameter buffer
+    DeviceState st;
+};
+
+template <class F, class R, int MODE>
+__global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __grid_constant__ QuadParams prm) {
+    const Plan& P = prm.P;
+    const DeviceState& st = prm.st;
+    // warp-private row-base buffers (ROTATE only), sized by rotate_smem_bytes()
+    extern __shared__ __align__(16) unsigned char sDyn[];
+    using Worker = PartWorker<F, R, MODE>;
+    Vec2<R>* const sSC = reinterpret_cast<Vec2<R>*>(sDyn);
+    double* const sX0 = reinterpret_cast<double*>(sDyn + sizeof(Vec2<R>) * (kThreads / 32) * 2 * Worker::kBufStride);
+    __shared__ dd sWarpTot[kBatchSlots][kThreads / 32];   // per-warp part totals, reduced once per batch
+    __shared__ dd sMine[kBatchSlots];                      // this CTA's part sums of the batch
+    __shared__ uint32_t sLo[kBatchSlots], sHi[kBatchSlots];   // tile range of each slot's part
+    __shared__ __align__(16) dd sMail[kBatchChunks];       // DSMEM mailbox (leader CTA)
+    __shared__ dd sSeg[kSegments];
+    __shared__ __align__(8) bq_result sRes;                // result block, assembled by lane 0 of the last warp
+    __shared__ int sIsLast;
+    constexpr bool kIsProfile = std::is_same<F, ProfileF>::value;
+    __shared__ __align__(16) double sTable[kIsProfile ? kMaxTable : 2];
+    __shared__ __align__(8) uint64_t sBar;
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const uint32_t crank = ptx::cluster_ctarank();
+    const uint32_t csize = ptx::cluster_nctarank();
+
+    if (blockIdx.x == 0 && tid == 0) st.result->t_start_ns = ptx::globaltimer();
+    uint64_t trace_t0 = 0, trace_tiles = 0;
+    if (st.trace && tid == 0) trace_t0 = ptx::globaltimer();
+
+    if (kIsProfile) {
+        // One 1-D TMA bulk copy brings the whole table (14.4 KB by default).
+        if (tid == 0) ptx::mbar_init(&sBar, 1);
+        __syncthreads();
+        const uint32_t bytes = ((P.table_len + 1u) & ~1u) * 8u;
+        if (tid == 0) {
+            ptx::mbar_expect_tx(&sBar, bytes);
+            ptx::tma_bulk_g2s(sTable, st.table, bytes, &sBar);
+        }
+        ptx::mbar_wait(&sBar, 0);
+    }
+
+    const F f = make_functor<F>(P, sTable);
+    const Worker worker(P, f, sSC + warp * 2 * Worker::kBufStride,
+                        sX0 + (F::kNeedX ? warp * 2 * Worker::kBufStride : 0));
+
+    const uint32_t cluster_id = blockIdx.x / csize;
+    const uint32_t n_clusters = gridDim.x / csize;
+
+    // ---- chunks ------------------------------------------------------------
+    // A cluster owns a contiguous run of chunks (for small n the few chunks that
+    // hold a tile are evenly spaced; a strided assignment would pile them onto a
+    // handful of clusters).  With a cluster pair, CTA q takes part q of every
+    // chunk.  Nothing in the tile loop synchronises beyond a warp: every warp
+    // parks its total of a part in shared memory and moves on, and the
+    // CTA-wide / cluster-wide combine happens once per batch of kBatchChunks
+    // chunks — one __syncthreads and one cluster barrier per launch on the
+    // default grid, instead of one of each per chunk.
+    const uint32_t per_cluster = (P.chunk_hi - P.chunk_lo + n_clusters - 1) / n_clusters;
+    const uint32_t my_lo = P.chunk_lo + cluster_id * per_cluster;
+    const uint32_t my_hi = my_lo + per_cluster < P.chunk_hi ? my_lo + per_cluster : P.chunk_hi;
+    const uint32_t pp = (csize == 2) ? 1u : uint32_t(kPartsPerChunk);   // parts per chunk done here
+    for (uint32_t b_lo = my_lo; b_lo < my_hi; b_lo += kBatchChunks) {
+        const uint32_t nb = my_hi - b_lo < uint32_t(kBatchChunks) ? my_hi - b_lo : uint32_t(kBatchChunks);
+        // Tile ranges of the batch's parts: one thread per slot works them out (two 64-bit
+        // divisions each) instead of every thread of the CTA repeating all of them — for small
+        // n, where most parts are empty, that repetition was most of a CTA's life.
+        if (uint32_t(tid) < nb * pp) {
+            const uint32_t k = uint32_t(tid) / pp, q = uint32_t(tid) % pp;
+            const uint32_t part = (b_lo + k) * kPartsPerChunk + (csize == 2 ? crank : q);
+            uint64_t lo, hi;
+            part_tiles(P, part, lo, hi);
+            sLo[tid] = uint32_t(lo), sHi[tid] = uint32_t(hi);   // n_tiles < 2^31
+        }
+        __syncthreads();
+        for (uint32_t slot = 0; slot < nb * pp; ++slot) {
+            const uint32_t lo = sLo[slot], hi = sHi[slot];
+            trace_tiles += hi - lo;
+            dd t{0.0, 0.0};
+            if (lo < hi) t = warp_reduce_lazy(worker.run(lo, hi));   // small n: most parts hold no tile
+            if (lane == 0) sWarpTot[slot][warp] = t;
+        }
+        __syncthreads();
+        // Part sums: warp w finishes slots w, w + 8 (the 8-lane butterfly + one
+        // renormalisation).
+        for (uint32_t s = warp; s < nb * pp; s += kThreads / 32) {
+            dd r = lane < kThreads / 32 ? sWarpTot[s][lane] : dd{0.0, 0.0};
+#pragma unroll
+            for (int off = 4; off >= 1; off >>= 1) r = dd_add_lazy(r, shfl_xor_dd(r, off));
+            r = dd_renorm(r);
+            if (lane == 0) {
+                if (csize == 2 && crank == 1)
+                    ptx::st_dsmem_f64x2(ptx::mapa(&sMail[s], 0), r.hi, r.lo);   // partner's mailbox
+                else
+                    sMine[s] = r;
+            }
+        }
+        if (csize == 2)
+            ptx::cluster_sync_all();    // mailbox complete (release/acquire), also a CTA barrier
+        else
+            __syncthreads();
+        if (crank == 0 && uint32_t(tid) < nb) {
+            const dd p0 = sMine[tid * pp];
+            const dd p1 = (csize == 2) ? sMail[tid] : sMine[tid * pp + 1];
+            st.partials[b_lo + tid] = dd_add(p0, p1);
+        }
+        if (b_lo + kBatchChunks < my_hi) {   // another batch reuses the slots and the mailbox
+            if (csize == 2)
+                ptx::cluster_sync_all();
+            else
+                __syncthreads();
+        }
+    }
+    if (st.trace && tid == 0) {
+        uint32_t smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        uint64_t* t = st.trace + 4 * blockIdx.x;
+        t[0] = trace_t0, t[1] = ptx::globaltimer(), t[2] = smid, t[3] = trace_tiles;
+    }
+    if (crank != 0) return;
+
+    // ---- ticket: who is last? ------------------------------------------------
+    __syncthreads();                 // every chunk sum of this cluster is stored
+    if (tid == 0) {
+        __threadfence();
+        const unsigned int t = atomicAdd(st.ticket, 1u);
+        sIsLast = (t == n_clusters - 1);
+    }
+    __syncthreads();
+    if (!sIsLast) return;
+    __threadfence();
+    // kernel-entry stamp of CTA 0 (ordered before this point by the ticket chain): fetched now so
+    // that the load is long done when the block is assembled
+    const uint64_t t_start = *reinterpret_cast<volatile const uint64_t*>(&st.result->t_start_ns);
+
+    // ---- segment sums: one warp per owned segment, fixed order ---------------
+    if (tid < kSegments) sSeg[tid] = dd{0.0, 0.0};
+    __syncthreads();
+    {
+        const uint32_t seg = P.seg_lo + warp;
+        if (seg < P.seg_hi) {
+            constexpr int kPerLane = (kChunksPerSegment + 31) / 32;
+            const uint32_t c0 = seg * kChunksPerSegment;
+            // all loads in flight first, then the same in-order fold as ever
+            double hi[kPerLane], lo[kPerLane];
+#pragma unroll
+            for (int i = 0; i < kPerLane; ++i) {
+                const uint32_t c = c0 + lane + 32 * i;
+                hi[i] = lo[i] = 0.0;
+                if (c < c0 + kChunksPerSegment)
+                    ptx::ld_relaxed_sys_f64x2(reinterpret_cast<const double*>(st.partials + c), hi[i], lo[i]);
+            }
+            dd acc{0.0, 0.0};
+#pragma unroll
+            for (int i = 0; i < kPerLane; ++i)
+                if (c0 + lane + 32 * i < c0 + kChunksPerSegment) acc = dd_add(acc, dd{hi[i], lo[i]});
+            acc = warp_reduce_dd(acc);
+            if (lane == 0) sSeg[seg] = acc;
+        }
+    }
+    __syncthreads();
+    if (warp != 0) return;
+
+    int status = BQ_OK;
+    const bool exchange = P.world > 1 && !(P.flags & kFlagLocalOnly);
+    if (exchange) {
+        // ---- cross-GPU: publish, barrier, gather -----------------------------
+        const uint64_t epoch = st.comm->epoch;
+        const int par = int(epoch & 1);
+        if (lane < P.world && !(P.flags & kFlagSkipPublish)) {
+            CommBlock* peer = st.peers[lane];
+            for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s)
+                ptx::st_relaxed_sys_f64x2(&peer->slots[par][s][0], sSeg[s].hi, sSeg[s].lo);
+            ptx::red_release_sys_add(&peer->arrived, 1ull);
+        }
+        __syncwarp();
+        const uint64_t target = uint64_t(P.world) * (epoch + 1);
+        const uint64_t t0 = ptx::globaltimer();
+        const uint64_t limit = uint64_t(P.timeout_ms) * 1000000ull;
+        if (lane == 0) {
+            while (ptx::ld_acquire_sys(&st.comm->arrived) < target) {
+                if (ptx::globaltimer() - t0 > limit) {
+                    status = BQ_ERR_TIMEOUT;
+                    break;
+                }
+            }
+        }
+        status = __shfl_sync(0xffffffffu, status, 0);
+        if (lane < kSegments) {
+            double hi, lo;
+            ptx::ld_relaxed_sys_f64x2(&st.comm->slots[par][lane][0], hi, lo);
+            sSeg[lane] = dd{hi, lo};
+        }
+        __syncwarp();
+        if (lane == 0) st.comm->epoch = epoch + 1;
+    }
+
+    // The result block is assembled in shared memory and leaves in two warp-wide bursts (device
+    // block, host block): no thread reads back what another one just stored to global memory.
+    if (lane == 0) {
+        double hi[kSegments], lo[kSegments];
+        for (int s = 0; s < kSegments; ++s) hi[s] = sSeg[s].hi, lo[s] = sSeg[s].lo;
+        if (st.seg_out) {
+            for (int s = 0; s < kSegments; ++s) st.seg_out[2 * s] = hi[s], st.seg_out[2 * s + 1] = lo[s];
+        }
+        finish_result<F>(P, f, hi, lo, &sRes);
+        if (status != BQ_OK) sRes.value = nan("");
+        if (st.value_out) *st.value_out = sRes.value;
+        sRes.t_start_ns = t_start;
+        sRes.status = status;
+        sRes.device_ms = 0.f;
+        sRes.seq = st.seq;
+        sRes.reserved = 0;
+        *st.ticket = 0u;
+        sRes.t_end_ns = ptx::globaltimer();
+    }
+    __syncwarp();
+    static_assert(sizeof(bq_result) % 8 == 0 && sizeof(bq_result) / 8 <= 32, "result block = one word per lane");
+    constexpr int kWords = int(sizeof(bq_result) / 8);
+    constexpr int kSeqWord = int(offsetof(bq_result, seq) / 8);
+    const unsigned long long word = lane < kWords ? reinterpret_cast<const unsigned long long*>(&sRes)[lane] : 0ull;
+    if (lane < kWords) reinterpret_cast<unsigned long long*>(st.result)[lane] = word;
+    // The device -> host leg of the call: the block goes straight into the context's pinned,
+    // mapped host block (a single PCIe write burst) — no copy engine operation follows the
+    // kernel.  The call number goes last, after a system-scope fence, so a host that watches
+    // that word sees a complete block.
+    if (st.result_host) {
+        volatile unsigned long long* dst = reinterpret_cast<volatile unsigned long long*>(st.result_host);
+        if (lane < kWords && lane != kSeqWord) dst[lane] = word;
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) dst[kSeqWord] = st.seq;
+    }
+}
+
+// ---- dispatch ----------------------------------------------------------------
+
+// Dynamic shared memory of one CTA: the warp-private row-base buffers of ROTATE.
+template <class F, class R, int MODE>
+constexpr size_t rotate_smem_bytes() {
+    using W = PartWorker<F, R, MODE>;
+    return MODE == BQ_EVAL_ROTATE
+               ? size_t(kThreads / 32) * 2 * W::kBufStride * (sizeof(Vec2<R>) + (F::kNeedX ? sizeof(double) : 0))
+               : 0;
+}
+
+template <class F, class R, int MODE>
+inline cudaError_t launch_one(const Plan& P, const DeviceState& st, const LaunchConfig& cfg, cudaStream_t stream) {
+    QuadParams prm;
+    prm.P = P;
+    prm.st = st;
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(cfg.grid, 1, 1);
+    lc.blockDim = dim3(kThreads, 1, 1);
+    lc.dynamicSmemBytes = rotate_smem_bytes<F, R, MODE>();
+    lc.stream = stream;
+    if (lc.dynamicSmemBytes > 48 * 1024) {
+        // above the default limit (only the double-precision x-dependent trig integrand): opt in,
+        // once per device
+        static bool done[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !done[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(quad_kernel<F, R, MODE>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 int(lc.dynamicSmemBytes));
+            if (e != cudaSuccess) return e;
+            done[dev] = true;
+        }
+    }
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cfg.cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    return cudaLaunchKernelEx(&lc, quad_kernel<F, R, MODE>, prm);
+}
+
+}  // namespace bq

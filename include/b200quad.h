@@ -26,7 +26,8 @@ enum bq_integrand {
     BQ_F_VEL = 2,
     BQ_F_DIS = 3,
     BQ_F_PROFILE = 4,
-    BQ_F_COUNT = 5
+    BQ_F_CUSTOM = 5,   /* user expression compiled into the same fused kernel (see below) */
+    BQ_F_COUNT = 6
 };
 
 /* Quadrature rule.  The reference only has LEFT (riemann.cpp:36-39). */
@@ -120,6 +121,21 @@ typedef struct bq_scan_result {
     float device_ms;
     uint64_t reserved[2];
 } bq_scan_result;
+
+/* ---- custom integrands --------------------------------------------------
+ * The reference hard-codes its integrand (riemann.cpp:37, cintegrate.cu:68).
+ * Here a C++ expression in x (and parameters p0..p3) can be compiled into the
+ * SAME fused kernel — evaluation, block/cluster reduction, cross-GPU combine —
+ * by a small translation unit that instantiates the kernel template for it
+ * (b200quad.models.custom(), models/jit.py, generates, builds and loads it).  That unit hands
+ * the library two entry points; jobs with integrand = BQ_F_CUSTOM then use them.
+ *   launch(plan, device_state, launch_config, stream) -> cudaError_t as int
+ *   eval(x, p[4])                                     -> f(x) on the host (CPU backend, oracles)
+ * One custom integrand is active per process at a time. */
+typedef int (*bq_custom_launch_fn)(const void* plan, const void* device_state, const void* launch_config,
+                                   void* stream);
+typedef double (*bq_custom_eval_fn)(double x, const double* p);
+int bq_set_custom_integrand(bq_custom_launch_fn launch, bq_custom_eval_fn eval);
 
 /* ---- library-level ----------------------------------------------------- */
 

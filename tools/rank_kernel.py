@@ -31,7 +31,7 @@ for world in (1, 2, 4, 8):
         assert rc == 0
         e1.record(stream)
         torch.cuda.synchronize()
-        r = ctx.fetch()
+        r = ctx.fetch_device()
         if it >= 2:
             best_dev = min(best_dev, e0.elapsed_time(e1) * 1e3)
             best_k = min(best_k, (r.t_end_ns - r.t_start_ns) / 1e3)
