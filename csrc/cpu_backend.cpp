@@ -8,6 +8,7 @@
 
 #include <atomic>
 #include <thread>
+#include <type_traits>
 #include <vector>
 
 #include "host_common.h"
@@ -105,21 +106,30 @@ struct CpuWorker {
                 const double* dxt = &dx[t * kCols];
                 TileAcc<R>& acc = accs[t];
                 double rb = row_base_index(P, g, 0);
+                constexpr bool fused = F::kFusedSum && std::is_same<R, double>::value;
                 for (uint32_t r = 0; r < g.full_rows; ++r) {
-                    R v[kCols];
-                    for (int j = 0; j < kCols; ++j)
-                        v[j] = rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j], X0[r], dxt[j])
-                                      : point_direct<F, R>(f, rb, dxt[j], P.h, P.a);
-                    acc.add_row(v);
+                    if (rotate && fused) {
+                        for (int j = 0; j < kCols; ++j) acc.add_rot(j, S[r], C[r], cjt[j], sjt[j]);
+                    } else {
+                        R v[kCols];
+                        for (int j = 0; j < kCols; ++j)
+                            v[j] = rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j], X0[r], dxt[j])
+                                          : point_direct<F, R>(f, rb, dxt[j], P.h, P.a);
+                        acc.add_row(v);
+                    }
                     rb += double(kWidth);
                 }
                 if (g.rem) {
                     const uint32_t r = g.full_rows;
                     for (int j = 0; j < kCols; ++j)
-                        if (uint32_t(t + kThreads * j) < g.rem)
-                            acc.add_one(j, rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j],
-                                                                       X0[r], dxt[j])
-                                                  : point_direct<F, R>(f, rb, dxt[j], P.h, P.a));
+                        if (uint32_t(t + kThreads * j) < g.rem) {
+                            if (rotate && fused)
+                                acc.add_rot(j, S[r], C[r], cjt[j], sjt[j]);
+                            else
+                                acc.add_one(j, rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j],
+                                                                           X0[r], dxt[j])
+                                                      : point_direct<F, R>(f, rb, dxt[j], P.h, P.a));
+                        }
                 }
                 if (((tile - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || tile + 1 == hi) {
                     total[t] = dd_acc_lazy(total[t], acc.flush());

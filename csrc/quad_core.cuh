@@ -72,6 +72,8 @@ struct TileAcc<double> {
         for (int j = 0; j < kCols; ++j) a[j] += v[j];
     }
     BQ_HD void add_one(int j, double v) { a[j] += v; }
+    // Fused accumulation of the sample S*cj + C*sj (integrands with kFusedSum): two chained FMAs.
+    BQ_HD void add_rot(int j, double S, double C, double cj, double sj) { a[j] = fma(C, sj, fma(S, cj, a[j])); }
     BQ_HD double flush() const { return pairwise_cols<double>(a); }
 };
 
@@ -83,6 +85,7 @@ struct TileAcc<float> {
         kahan_add(sum, comp, pairwise_cols<float>(v));
     }
     BQ_HD void add_one(int, float v) { kahan_add(sum, comp, v); }
+    BQ_HD void add_rot(int, float, float, float, float) {}   // fp32 keeps explicit samples (Kahan needs them)
     BQ_HD double flush() const { return double(sum) - double(comp); }
 };
 

@@ -27,8 +27,12 @@
 #include "quad_core.cuh"
 #include "quad_launch.h"
 
-// Rows of the ROTATE loop unrolled together.  Measured on B200 at n = 2^32 (fp64 / fp32,
-// G intervals/s): 2: 5458 / 8281, 4: 5528 / 8660, 8: 5645 / 8684, 16: 5702 / 8616.
+// Rows of the ROTATE loop unrolled together.  Measured on B200 at n = 2^32, G intervals/s:
+//   3-instruction loop (fp64 / fp32):  2: 5458 / 8281, 4: 5528 / 8660, 8: 5645 / 8684, 16: 5702 / 8616
+//   fused 2-DFMA loop (fp64, SinF):    8: 7274, 16: 7374, 32: 7429; a second accumulator set per
+//   column (16 / 8 rows): 7200 / 7079.  Pinning the column constants to aligned register quads
+//   (so that constant and accumulator of a DFMA sit in different register banks) changed
+//   nothing (7421): the loop is not limited by register-bank conflicts.
 #ifndef BQ_ROT_UNROLL
 #define BQ_ROT_UNROLL 16
 #endif
@@ -77,6 +81,7 @@ __device__ __forceinline__ dd warp_reduce_lazy(dd v) {
 template <class F, class R, int MODE>
 struct PartWorker {
     static constexpr bool kRotate = (MODE == BQ_EVAL_ROTATE);
+    static constexpr bool kFused = F::kFusedSum && std::is_same<R, double>::value;   // see SinF
 
     const Plan& P;        // kernel parameter (constant bank)
     const F& f;
@@ -176,11 +181,16 @@ struct PartWorker {
         for (Count r = 0; r < nrows; ++r) {
             const Vec2<R> sc_next = sc_row[r + 1];
             const double x0_next = F::kNeedX ? x0_row[r + 1] : 0.0;
-            R v[kCols];
+            if constexpr (kFused) {
 #pragma unroll
-            for (int j = 0; j < kCols; ++j)
-                v[j] = point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]);
-            acc.add_row(v);
+                for (int j = 0; j < kCols; ++j) acc.add_rot(j, sc.x, sc.y, cj[j], sj[j]);
+            } else {
+                R v[kCols];
+#pragma unroll
+                for (int j = 0; j < kCols; ++j)
+                    v[j] = point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]);
+                acc.add_row(v);
+            }
             sc = sc_next;
             x0 = x0_next;
         }
@@ -200,8 +210,12 @@ struct PartWorker {
         if (rem) {   // sc / x0 already hold row full_rows
 #pragma unroll
             for (int j = 0; j < kCols; ++j)
-                if (threadIdx.x + kThreads * j < rem)
-                    acc.add_one(j, point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]));
+                if (threadIdx.x + kThreads * j < rem) {
+                    if constexpr (kFused)
+                        acc.add_rot(j, sc.x, sc.y, cj[j], sj[j]);
+                    else
+                        acc.add_one(j, point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]));
+                }
         }
     }
 
