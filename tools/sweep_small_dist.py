@@ -47,7 +47,8 @@ def timed(step):
         step()
         e1.record(stream)
     torch.cuda.synchronize(dev)
-    t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs) / K * 1e3], dtype=torch.float64, device=dev)
+    per = sorted(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([per[len(per) // 2] * 1e3], dtype=torch.float64, device=dev)   # median: one-off spikes out
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t)
 
