@@ -67,8 +67,15 @@ struct CpuWorker {
                 const int idx = t * kCols + j;
                 if (rotate) {
                     const SinCos cs = rotate_sc(mine, blk[j]);
-                    cj[idx] = R(cs.c);
-                    sj[idx] = R(cs.s);
+                    if (F::kFusedSum && std::is_same<R, double>::value) {
+                        double Pc, Qc;
+                        fused_consts(f, cs, Pc, Qc);
+                        cj[idx] = R(Pc);
+                        sj[idx] = R(Qc);
+                    } else {
+                        cj[idx] = R(cs.c);
+                        sj[idx] = R(cs.s);
+                    }
                     dx[idx] = double(t + kThreads * j) * P.h;
                 } else {
                     cj[idx] = R(0);

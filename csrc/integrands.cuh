@@ -34,6 +34,10 @@ struct SinF {
     // chained FMAs (acc = fma(C, sj, fma(S, cj, acc))) instead of being rounded to a double first
     // and added: 2 fp64 instructions per interval instead of 3, one rounding fewer per term.
     static constexpr bool kFusedSum = true;
+    // f = alpha * sin(angle) + beta * cos(angle) + gamma (what the fused loop needs, see fused_consts)
+    BQ_HD double fuse_alpha() const { return 1.0; }
+    BQ_HD double fuse_beta() const { return 0.0; }
+    BQ_HD double fuse_gamma() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return bq_sin(x); }
     BQ_HD double angle(double x) const { return x; }
@@ -42,9 +46,12 @@ struct SinF {
 };
 
 struct AccF {
-    static constexpr bool kFusedSum = false;
+    static constexpr bool kFusedSum = true;     // -ascale * sin
     static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = false;
     double tscale, ascale;
+    BQ_HD double fuse_alpha() const { return -ascale; }
+    BQ_HD double fuse_beta() const { return 0.0; }
+    BQ_HD double fuse_gamma() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return -(bq_sin(x / R(tscale)) * R(ascale)); }
     BQ_HD double angle(double x) const { return x / tscale; }
@@ -53,9 +60,12 @@ struct AccF {
 };
 
 struct VelF {
-    static constexpr bool kFusedSum = false;
+    static constexpr bool kFusedSum = true;     // vscale - vscale * cos: the constant is added once, as gamma * n
     static constexpr bool kTrig = true, kNeedS = false, kNeedC = true, kNeedX = false;
     double tscale, vscale;
+    BQ_HD double fuse_alpha() const { return 0.0; }
+    BQ_HD double fuse_beta() const { return -vscale; }
+    BQ_HD double fuse_gamma() const { return vscale; }
     template <class R>
     BQ_HD R eval(R x) const { return (-bq_cos(x / R(tscale)) + R(1)) * R(vscale); }
     BQ_HD double angle(double x) const { return x / tscale; }
@@ -65,6 +75,9 @@ struct VelF {
 
 struct DisF {
     static constexpr bool kFusedSum = false;
+    BQ_HD double fuse_alpha() const { return 0.0; }
+    BQ_HD double fuse_beta() const { return 0.0; }
+    BQ_HD double fuse_gamma() const { return 0.0; }
     static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = true;
     double tscale, vscale;
     template <class R>
@@ -81,6 +94,9 @@ struct DisF {
 // the edge cell linearly (the kernel flags it as BQ_ERR_RANGE).
 struct ProfileF {
     static constexpr bool kFusedSum = false;
+    BQ_HD double fuse_alpha() const { return 0.0; }
+    BQ_HD double fuse_beta() const { return 0.0; }
+    BQ_HD double fuse_gamma() const { return 0.0; }
     static constexpr bool kTrig = false, kNeedS = false, kNeedC = false, kNeedX = true;
     const double* table;
     int len;
@@ -107,6 +123,9 @@ struct ProfileF {
 // compiled into the kernel (b200quad/models/jit.py generates that unit).
 struct CustomHostF {
     static constexpr bool kFusedSum = false;
+    BQ_HD double fuse_alpha() const { return 0.0; }
+    BQ_HD double fuse_beta() const { return 0.0; }
+    BQ_HD double fuse_gamma() const { return 0.0; }
     static constexpr bool kTrig = false, kNeedS = false, kNeedC = false, kNeedX = true;
     double (*fn)(double, const double*);
     double p[4];

@@ -44,6 +44,18 @@ BQ_HD R point_direct(const F& f, double rowbase, double col, double h, double a)
     return f.template eval<R>(R(x));
 }
 
+// Fused accumulation (integrands with kFusedSum, fp64 ROTATE).  For f = alpha*s + beta*c + gamma
+// with s = S*cj + C*sj, c = C*cj - S*sj the sample is S*P + C*Q + gamma with the per-column
+// constants P = alpha*cj - beta*sj, Q = alpha*sj + beta*cj, so the loop is two chained FMAs,
+// acc = fma(C, Q, fma(S, P, acc)), whatever the linear combination; gamma enters once, as
+// gamma * n, in finish_result.  (alpha, beta) = (1, 0) leaves cj, sj unchanged bit for bit.
+template <class F>
+BQ_HD void fused_consts(const F& f, SinCos col, double& P, double& Q) {
+    const double al = f.fuse_alpha(), be = f.fuse_beta();
+    P = al * col.c - be * col.s;
+    Q = al * col.s + be * col.c;
+}
+
 // Per-thread, per-tile accumulator.
 //   fp64: kCols independent naive sums (<= kMaxRows terms each), combined
 //         pairwise and pushed into the thread's dd total at the end of a tile.
@@ -144,6 +156,8 @@ BQ_HDI void finish_result(const Plan& P, const F& f, const double* seg_hi, const
                           bq_result* out) {
     dd acc{0.0, 0.0};
     for (int s = 0; s < kSegments; ++s) acc = dd_add(acc, dd{seg_hi[s], seg_lo[s]});
+    if (F::kFusedSum && P.eval == BQ_EVAL_ROTATE && P.dtype == BQ_F64 && f.fuse_gamma() != 0.0)
+        acc = dd_add(acc, dd_mul_d(dd{double(P.n), 0.0}, f.fuse_gamma()));   // the constant term of every sample
     dd val = dd_mul_d(acc, P.h);
     if (P.rule == BQ_RULE_TRAP) {
         double fb = f.template eval<double>(P.b);

@@ -111,8 +111,15 @@ struct PartWorker {
                 bj.s = __shfl_sync(0xffffffffu, blk.s, j);
                 bj.c = __shfl_sync(0xffffffffu, blk.c, j);
                 const SinCos cs = rotate_sc(mine, bj);
-                cj[j] = R(cs.c);
-                sj[j] = R(cs.s);
+                if constexpr (kFused) {
+                    double Pc, Qc;
+                    fused_consts(f, cs, Pc, Qc);
+                    cj[j] = R(Pc);
+                    sj[j] = R(Qc);
+                } else {
+                    cj[j] = R(cs.c);
+                    sj[j] = R(cs.s);
+                }
                 dx[j] = double(threadIdx.x + kThreads * j) * h;
             }
             sincos(f.angle(double(lane) * double(kWidth) * h), &rowrot.s, &rowrot.c);
