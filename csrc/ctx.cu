@@ -1,4 +1,4 @@
-// CUDA host runtime: contexts, pinned staging, peer wiring, launches.
+// CUDA host runtime: contexts, pinned result blocks, peer wiring, launches.
 //
 // The reference's host side is three main()s that cudaMalloc/cudaMemcpy 144 MB
 // of uninitialised memory per run and never check an error
@@ -71,7 +71,6 @@ int bq_ctx_create(int device, bq_ctx** out) {
     cudaDeviceProp prop;
     BQ_CUDA(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
-    c->cc_major = prop.major;
     BQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     BQ_CUDA(cudaEventCreate(&c->ev0));
     BQ_CUDA(cudaEventCreate(&c->ev1));
@@ -88,7 +87,6 @@ int bq_ctx_create(int device, bq_ctx** out) {
     BQ_CUDA(cudaMemset(c->d_comm, 0, sizeof(CommBlock)));
     BQ_CUDA(cudaMalloc(&c->d_table, sizeof(double) * (kMaxTable + 2)));
     BQ_CUDA(cudaMemset(c->d_table, 0, sizeof(double) * (kMaxTable + 2)));
-    BQ_CUDA(cudaMalloc(&c->d_seg_scratch, sizeof(double) * 2 * kSegments));
 
     BQ_CUDA(cudaHostAlloc(&c->h_result, sizeof(bq_result), cudaHostAllocMapped));
     BQ_CUDA(cudaHostGetDevicePointer((void**)&c->h_result_dev, c->h_result, 0));
@@ -123,7 +121,6 @@ void bq_ctx_destroy(bq_ctx* c) {
     cudaFree(c->d_scan_result);
     cudaFree(c->d_comm);
     cudaFree(c->d_table);
-    cudaFree(c->d_seg_scratch);
     cudaFree(c->d_trace);
     cudaFreeHost(c->h_result);
     cudaFreeHost(c->h_scan_result);

@@ -15,7 +15,6 @@ namespace bq {
 struct bq_ctx {
     int device = 0;
     int sm_count = 0;
-    int cc_major = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t last_stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -34,7 +33,6 @@ struct bq_ctx {
     bq_scan_result* d_scan_result = nullptr;
     bq::CommBlock* d_comm = nullptr;
     double* d_table = nullptr;
-    double* d_seg_scratch = nullptr;
     uint64_t* d_trace = nullptr;          // per-CTA timeline, allocated by bq_ctx_trace(on)
     int trace_ctas = 0;
     int table_len = 0;

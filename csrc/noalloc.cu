@@ -10,7 +10,7 @@
 // scratch that grows with n; this one allocates nothing, ever.
 //
 // How: the scratch of the fused scan kernel (tile aggregates, tile prefixes,
-// segment bases, tickets, flag words, the parameter block, the result block
+// segment bases, tickets, flag words, the result block
 // and a copy of the velocity table) lives in ONE file-scope
 // `static __device__ __align__(256)` array below.  Its size is fixed at build
 // time, which is what bounds n (BQ_NOALLOC_MAX_SAMPLES).  Every GPU that loads
@@ -58,7 +58,6 @@ struct NoAllocControl {
 
 struct NoAllocScratch {
     NoAllocControl control;
-    ScanPlan plan;                    // parameter block of the call in flight
     alignas(32) double segbase[4 * kSegments];
     alignas(32) double table[kMaxTable + 2];      // PROFILE table (default ex4vel.h values)
     alignas(32) double agg[2 * kNoAllocMaxTiles];
@@ -173,13 +172,10 @@ int bq_cumulative_noalloc(int device, const bq_scan_job* job, double* dP, double
     NoAllocScratch* sc = s->scratch;
     // The shared array still holds the previous call's state: zero what must start at zero.
     BQ_NA_CUDA(cudaMemsetAsync(&sc->control, 0, sizeof(NoAllocControl), st));
-    // Parameter block: `plan` is pageable host memory, which the runtime stages
-    // before cudaMemcpyAsync returns, so the stack copy may go out of scope.
-    BQ_NA_CUDA(cudaMemcpyAsync(&sc->plan, &plan, sizeof(ScanPlan), cudaMemcpyHostToDevice, st));
+    // (The parameter block itself travels in the kernel's launch parameters.)
 
     ScanState state;
     memset(&state, 0, sizeof(state));
-    state.plan = &sc->plan;
     state.agg = sc->agg;
     state.prefix = sc->prefix;
     state.segbase = sc->segbase;

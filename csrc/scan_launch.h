@@ -8,7 +8,6 @@
 namespace bq {
 
 struct ScanState {
-    const ScanPlan* plan;     // unused by the kernel (the plan rides in the launch parameters)
     double* agg;              // [rank tiles][2]  tile aggregates (sum v, sum of local P)
     double* prefix;           // [rank tiles][4]  exclusive prefix inside the segment (dd P, dd Q)
     double* segbase;          // [kSegments][4]   exclusive prefix of each segment (dd P, dd Q)
