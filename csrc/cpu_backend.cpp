@@ -67,7 +67,7 @@ struct CpuWorker {
                 const int idx = t * kCols + j;
                 if (rotate) {
                     const SinCos cs = rotate_sc(mine, blk[j]);
-                    if (F::kFusedSum && std::is_same<R, double>::value) {
+                    if (F::kFusedSum) {
                         double Pc, Qc;
                         fused_consts(f, cs, Pc, Qc);
                         cj[idx] = R(Pc);
@@ -113,10 +113,11 @@ struct CpuWorker {
                 const double* dxt = &dx[t * kCols];
                 TileAcc<R>& acc = accs[t];
                 double rb = row_base_index(P, g, 0);
-                constexpr bool fused = F::kFusedSum && std::is_same<R, double>::value;
+                constexpr bool fused = F::kFusedSum;
                 for (uint32_t r = 0; r < g.full_rows; ++r) {
                     if (rotate && fused) {
                         for (int j = 0; j < kCols; ++j) acc.add_rot(j, S[r], C[r], cjt[j], sjt[j]);
+                        if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();
                     } else {
                         R v[kCols];
                         for (int j = 0; j < kCols; ++j)
@@ -139,7 +140,7 @@ struct CpuWorker {
                         }
                 }
                 if (((tile - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || tile + 1 == hi) {
-                    total[t] = dd_acc_lazy(total[t], acc.flush());
+                    total[t] = dd_acc_lazy(total[t], (rotate && fused) ? acc.flush_fused() : acc.flush());
                     acc.clear();
                 }
             }

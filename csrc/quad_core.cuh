@@ -44,7 +44,7 @@ BQ_HD R point_direct(const F& f, double rowbase, double col, double h, double a)
     return f.template eval<R>(R(x));
 }
 
-// Fused accumulation (integrands with kFusedSum, fp64 ROTATE).  For f = alpha*s + beta*c + gamma
+// Fused accumulation (integrands with kFusedSum, ROTATE, both precisions).  For f = alpha*s + beta*c + gamma
 // with s = S*cj + C*sj, c = C*cj - S*sj the sample is S*P + C*Q + gamma with the per-column
 // constants P = alpha*cj - beta*sj, Q = alpha*sj + beta*cj, so the loop is two chained FMAs,
 // acc = fma(C, Q, fma(S, P, acc)), whatever the linear combination; gamma enters once, as
@@ -86,20 +86,45 @@ struct TileAcc<double> {
     BQ_HD void add_one(int j, double v) { a[j] += v; }
     // Fused accumulation of the sample S*cj + C*sj (integrands with kFusedSum): two chained FMAs.
     BQ_HD void add_rot(int j, double S, double C, double cj, double sj) { a[j] = fma(C, sj, fma(S, cj, a[j])); }
+    BQ_HD void promote() {}
     BQ_HD double flush() const { return pairwise_cols<double>(a); }
+    BQ_HD double flush_fused() { return pairwise_cols<double>(a); }
 };
 
 template <>
 struct TileAcc<float> {
+    // sample-by-sample integrands: Kahan in fp32 over the pairwise row sums
     float sum, comp;
-    BQ_HD void clear() { sum = 0.f, comp = 0.f; }
+    // fused integrands: fp32 FMA runs of at most kPromoteRows rows per column, promoted to fp64
+    // (the fp64 adds ride on the otherwise idle fp64 pipe; error of a run <= ~16 ulp_fp32(|run|),
+    // random in sign, so it averages out over the millions of runs of a large n)
+    float a[kCols];
+    double d[kCols];
+    BQ_HD void clear() {
+        sum = 0.f, comp = 0.f;
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) a[j] = 0.f, d[j] = 0.0;
+    }
     BQ_HD void add_row(const float (&v)[kCols]) {
         kahan_add(sum, comp, pairwise_cols<float>(v));
     }
     BQ_HD void add_one(int, float v) { kahan_add(sum, comp, v); }
-    BQ_HD void add_rot(int, float, float, float, float) {}   // fp32 keeps explicit samples (Kahan needs them)
+    BQ_HD void add_rot(int j, float S, float C, float P, float Q) { a[j] = fmaf(C, Q, fmaf(S, P, a[j])); }
+    BQ_HD void promote() {
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) d[j] += double(a[j]), a[j] = 0.f;
+    }
     BQ_HD double flush() const { return double(sum) - double(comp); }
+    BQ_HD double flush_fused() {
+        promote();
+        return pairwise_cols<double>(d);
+    }
 };
+
+#ifndef BQ_PROMOTE_ROWS
+#define BQ_PROMOTE_ROWS 16
+#endif
+constexpr int kPromoteRows = BQ_PROMOTE_ROWS;   // fused fp32: rows summed in fp32 before the promotion to fp64
 
 // Geometry of one tile.
 struct TileGeom {
@@ -156,7 +181,7 @@ BQ_HDI void finish_result(const Plan& P, const F& f, const double* seg_hi, const
                           bq_result* out) {
     dd acc{0.0, 0.0};
     for (int s = 0; s < kSegments; ++s) acc = dd_add(acc, dd{seg_hi[s], seg_lo[s]});
-    if (F::kFusedSum && P.eval == BQ_EVAL_ROTATE && P.dtype == BQ_F64 && f.fuse_gamma() != 0.0)
+    if (F::kFusedSum && P.eval == BQ_EVAL_ROTATE && f.fuse_gamma() != 0.0)
         acc = dd_add(acc, dd_mul_d(dd{double(P.n), 0.0}, f.fuse_gamma()));   // the constant term of every sample
     dd val = dd_mul_d(acc, P.h);
     if (P.rule == BQ_RULE_TRAP) {

@@ -37,7 +37,7 @@
 #define BQ_ROT_UNROLL 16
 #endif
 #ifndef BQ_ROT_UNROLL_F32
-#define BQ_ROT_UNROLL_F32 8
+#define BQ_ROT_UNROLL_F32 16    // = kPromoteRows: the promotion lands at the end of an unrolled body
 #endif
 #ifndef BQ_MIN_CTAS
 #define BQ_MIN_CTAS 2
@@ -81,7 +81,7 @@ __device__ __forceinline__ dd warp_reduce_lazy(dd v) {
 template <class F, class R, int MODE>
 struct PartWorker {
     static constexpr bool kRotate = (MODE == BQ_EVAL_ROTATE);
-    static constexpr bool kFused = F::kFusedSum && std::is_same<R, double>::value;   // see SinF
+    static constexpr bool kFused = F::kFusedSum;   // see SinF / fused_consts
 
     const Plan& P;        // kernel parameter (constant bank)
     const F& f;
@@ -191,6 +191,7 @@ struct PartWorker {
             if constexpr (kFused) {
 #pragma unroll
                 for (int j = 0; j < kCols; ++j) acc.add_rot(j, sc.x, sc.y, cj[j], sj[j]);
+                if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();   // fp32 only; no-op in fp64
             } else {
                 R v[kCols];
 #pragma unroll
@@ -287,7 +288,7 @@ struct PartWorker {
                     for (uint32_t k = 0; k < nt; ++k)
                         tile_rotate(t + k, sc_row + k * kMaxRows, x0_row + k * kMaxRows, acc);
                 }
-                total = dd_acc_lazy(total, acc.flush());
+                total = dd_acc_lazy(total, kFused ? acc.flush_fused() : acc.flush());
                 acc.clear();
                 __syncwarp();
                 buf ^= 1;
