@@ -34,8 +34,9 @@ enum bq_integrand {
 enum bq_rule { BQ_RULE_LEFT = 0, BQ_RULE_RIGHT = 1, BQ_RULE_MID = 2, BQ_RULE_TRAP = 3 };
 
 /* Arithmetic.  F64: fp64 evaluation, dd-compensated combines.  F32C: fp32
- * evaluation with pairwise+Kahan per-thread accumulation, promoted to fp64 at
- * the first cross-thread combine. */
+ * evaluation; per-thread accumulation is compensated — fp32 FMA runs of 16
+ * samples promoted to fp64 (trig integrands in ROTATE mode) or pairwise + Kahan
+ * (everything else) — and every cross-thread combine is dd like in F64. */
 enum bq_dtype { BQ_F64 = 0, BQ_F32C = 1 };
 
 /* How f is evaluated.  DIRECT: x_i formed and f(x_i) called per point (works
