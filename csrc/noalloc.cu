@@ -6,7 +6,7 @@
 // inside a host application that owns all device memory and hands out only
 // fixed input/output buffers; a process running close to the memory limit
 // where an allocation can simply fail.  The regular entry points
-// (bq_cumulative, bq_ctx_create) allocate a context, a pinned staging ring and
+// (bq_cumulative, bq_ctx_create) allocate a context, pinned result blocks and
 // scratch that grows with n; this one allocates nothing, ever.
 //
 // How: the scratch of the fused scan kernel (tile aggregates, tile prefixes,

@@ -145,7 +145,7 @@ def test_launch_shape_does_not_change_bits():
 def test_back_to_back_async_calls():
     ctx = parallel.context()
     job = bq.make_job("sin", 0.0, math.pi, 1 << 22, "mid")
-    for _ in range(300):                   # more than the 64-slot staging ring
+    for _ in range(300):                   # many launches in flight on one stream
         ctx.integrate_async(job)
     r = ctx.fetch()
     assert r.status == 0 and rel(r.value, oracle_sin(0.0, math.pi, 1 << 22, "mid")) < 1e-15
