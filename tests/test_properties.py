@@ -1,0 +1,62 @@
+"""Property tests on the CPU backend (it walks the same summation tree as the sm_100a kernel, and
+the GPU tier asserts GPU == CPU bit for bit, so what holds here holds for the kernel's arithmetic)."""
+import ctypes as C
+import math
+
+from hypothesis import given, settings, strategies as st
+
+import b200quad as bq
+from b200quad import _native
+from b200quad.utils import oracle_sin
+
+RULES = ["left", "right", "mid", "trap"]
+
+
+@settings(max_examples=60, deadline=None)
+@given(n=st.integers(min_value=1, max_value=300_000), rule=st.sampled_from(RULES),
+       ev=st.sampled_from(["direct", "rotate"]),
+       a=st.floats(min_value=-3.0, max_value=3.0), width=st.floats(min_value=1e-3, max_value=6.0))
+def test_sin_any_interval_matches_closed_form(n, rule, ev, a, width):
+    b = a + width
+    r = bq.integrate_result("sin", a, b, n, rule, eval=ev, backend="cpu")
+    ref = oracle_sin(a, b, n, rule)
+    # the Riemann sum may cancel (e.g. around a zero of the integral): bound against the sum of |terms|
+    scale = max(abs(ref), width * 0.05, 1e-300)
+    assert r.status == 0
+    assert abs(r.value - ref) <= 4e-15 * scale + 1e-18, (r.value, ref)
+
+
+@settings(max_examples=25, deadline=None)
+@given(n=st.integers(min_value=1, max_value=200_000), rule=st.sampled_from(RULES),
+       name=st.sampled_from(["sin", "vel", "profile"]), world=st.sampled_from([2, 4, 8]))
+def test_any_world_size_reassembles_the_same_bits(n, rule, name, world):
+    """Segments computed rank by rank (as the ranks of a world would) fold to the single-rank bits."""
+    lib, _ = _native.load()
+    a, b = (0.0, math.pi) if name == "sin" else (0.0, 1800.0)
+    job = bq.make_job(name, a, b, n, rule)
+    whole = _native.Result()
+    assert lib.bq_cpu_integrate(C.byref(job), 2, C.byref(whole)) == 0
+    hi = (C.c_double * 8)()
+    lo = (C.c_double * 8)()
+    for rank in range(world):
+        part = _native.Result()
+        assert lib.bq_cpu_integrate_segments(C.byref(job), rank, world, 1, C.byref(part)) == 0
+        for s in range(rank * (8 // world), (rank + 1) * (8 // world)):
+            hi[s], lo[s] = part.seg_hi[s], part.seg_lo[s]
+    folded = _native.Result()
+    assert lib.bq_fold_segments(C.byref(job), hi, lo, C.byref(folded)) == 0
+    assert folded.value == whole.value and folded.value_lo == whole.value_lo
+
+
+@settings(max_examples=20, deadline=None)
+@given(n=st.integers(min_value=1, max_value=60_000), x0=st.floats(min_value=0.0, max_value=100.0),
+       dx=st.floats(min_value=1e-4, max_value=2e-2))
+def test_cumulative_tables_are_running_sums(n, x0, dx):
+    import torch
+    c = bq.cumulative_integrate("profile", x0, dx, n, want_samples=True, backend="cpu")
+    v = c.samples
+    P = torch.cumsum(v, 0)
+    Q = torch.cumsum(P, 0)
+    assert torch.allclose(c.P, P, rtol=1e-13, atol=1e-9)
+    assert torch.allclose(c.Q, Q, rtol=1e-12, atol=1e-6)
+    assert c.p_last == float(c.P[-1]) and c.q_last == float(c.Q[-1])
