@@ -92,8 +92,11 @@ inline int cpu_threads(const Args& a) {
     return int(a.getu("--threads", uint64_t(n > 0 ? n : 1)));
 }
 
-// integrate on `world` GPUs (0 = CPU backend); returns rank 0's result.
-inline int run_integrate(const bq_job& job, int world, int threads, bq_result* out) {
+// integrate on `world` GPUs (0 = CPU backend); returns rank 0's result.  The first launch of a
+// process also pays for loading the kernel image; with `steady_ms` the same job is launched once
+// more and *steady_ms gets that second launch's device time (max over ranks) — what --json reports
+// next to the first-call wall time of the legacy line.
+inline int run_integrate(const bq_job& job, int world, int threads, bq_result* out, float* steady_ms = nullptr) {
     if (world == 0) return bq_cpu_integrate(&job, threads, out);
     bq_world* w = nullptr;
     int rc = bq_world_create(world, nullptr, &w);
@@ -104,6 +107,14 @@ inline int run_integrate(const bq_job& job, int world, int threads, bq_result* o
     float ms = 0.f;
     for (int r = 0; r < world; ++r) ms = res[r].device_ms > ms ? res[r].device_ms : ms;
     out->device_ms = ms;
+    if (rc == BQ_OK && steady_ms) {
+        bq_result again[BQ_MAX_WORLD];
+        if (bq_world_integrate(w, &job, again) == BQ_OK) {
+            float m2 = 0.f;
+            for (int r = 0; r < world; ++r) m2 = again[r].device_ms > m2 ? again[r].device_ms : m2;
+            *steady_ms = m2;
+        }
+    }
     bq_world_destroy(w);
     return rc;
 }
