@@ -36,7 +36,10 @@ class Result(C.Structure):
                 ("t_end_ns", C.c_uint64), ("n", C.c_uint64), ("status", C.c_int32),
                 ("eval_used", C.c_int32), ("world", C.c_int32), ("rank", C.c_int32),
                 ("device_ms", C.c_float), ("launches", C.c_int32), ("seq", C.c_uint64),
-                ("reserved", C.c_uint64)]
+                ("reserved", C.c_uint64), ("stamp_ns", C.c_uint32 * 8)]
+
+
+STAMPS = ("prologue", "tiles", "ticket", "fold", "published", "barrier", "result", "spins")
 
 
 class ScanJob(C.Structure):
@@ -72,6 +75,8 @@ def _declare(lib, cuda):
     sig("bq_default_profile", P(dbl), P(i32))
     sig("bq_oracle_sin_sum", dbl, dbl, dbl, u64, i32)
     sig("bq_sizeof_params", C.c_size_t)
+    sig("bq_sin_bounded", dbl, dbl)
+    sig("bq_cos_bounded", dbl, dbl)
     sig("bq_set_custom_integrand", i32, vp, vp)
     sig("bq_cpu_integrate", i32, P(Job), i32, P(Result))
     sig("bq_cpu_integrate_segments", i32, P(Job), i32, i32, i32, P(Result))

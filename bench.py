@@ -31,8 +31,14 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# riemann_sum, 1e9 steps, 1 worker (survey box, -O0 as the Makefile builds it).
-BASELINE_G_INTERVALS = 0.0765
+# the reference's own `riemann` (unmodified, built as its Makefile does) measured on the
+# host CPUs of the same B200 box at W = N workers (`mpirun -n N+1`), G intervals/s.  vs_baseline
+# divides by the row of the matching worker count.
+BASELINE_G_INTERVALS_BY_WORKERS = {1: 0.139, 2: 0.249, 4: 0.422, 8: 0.820}
+
+
+def baseline_for(gpus):
+    return BASELINE_G_INTERVALS_BY_WORKERS.get(int(gpus), BASELINE_G_INTERVALS_BY_WORKERS[1])
 
 
 def parse():
@@ -57,7 +63,7 @@ def parse():
 def run_reference(args):
     from baseline import reference_arm
     if int(os.environ.get("RANK", "0")) == 0:
-        emit(reference_arm.run(args.gpus, args.steps, args.warmup))
+        emit(reference_arm.run(args.gpus, args.steps, args.warmup, args.log2n))
     return 0
 
 
@@ -194,7 +200,7 @@ def main():
             "metric": "G intervals/sec at N=2^%d (time-to-solution = ms_per_step)" % args.log2n,
             "value": value, "unit": "Gintervals/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": value / BASELINE_G_INTERVALS,
+            "scaling": "strong", "vs_baseline": value / baseline_for(args.gpus),
             "dtype": args.dtype, "data": "synthetic (analytic integrand, no input tensors)",
             "impl": "b200quad",
             "config": {"model": "integrate(%s, %g, %g, n=2^%d, rule=%s)" % (
@@ -202,7 +208,8 @@ def main():
                        "global_batch": n, "seq_len": n // args.gpus,
                        "parallelism": "dp%d (interval decomposition, in-kernel NVLink combine)" % args.gpus,
                        "eval": last.eval, "l2": "flushed between steps (256 MiB memset, untimed)",
-                       "baseline": "BASELINE.md riemann_sum 1 worker 0.0765 Gintervals/s (survey box)"},
+                       "baseline": "BASELINE.md: reference riemann on the same box, %d worker(s): %.3f Gintervals/s"
+                                   % (args.gpus, baseline_for(args.gpus))},
             "e2e": {"value": e2e_value, "unit": "Gintervals/s",
                     "ms_per_step": e2e_ms / args.steps,
                     "h2d_bytes_per_step": bytes_h2d(), "d2h_bytes_per_step": bytes_d2h(),
@@ -306,7 +313,7 @@ def bench_local_world(args, bq, parallel, job, n, torch):
         "metric": "G intervals/sec at N=2^%d (time-to-solution = ms_per_step)" % args.log2n,
         "value": value, "unit": "Gintervals/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": value / BASELINE_G_INTERVALS, "dtype": args.dtype,
+        "scaling": "strong", "vs_baseline": value / baseline_for(args.gpus), "dtype": args.dtype,
         "data": "synthetic (analytic integrand, no input tensors)", "impl": "b200quad",
         "config": {"model": "integrate(%s, n=2^%d, rule=%s)" % (args.integrand, args.log2n, args.rule),
                    "global_batch": n, "seq_len": n // args.gpus,

@@ -114,15 +114,23 @@ struct CpuWorker {
                 TileAcc<R>& acc = accs[t];
                 double rb = row_base_index(P, g, 0);
                 constexpr bool fused = F::kFusedSum;
+                const bool fast = F::kTrig && (P.flags & kFlagFastTrig);
+                double dcol[kCols];
+                for (int j = 0; j < kCols; ++j) dcol[j] = dxt[j];
                 for (uint32_t r = 0; r < g.full_rows; ++r) {
                     if (rotate && fused) {
                         for (int j = 0; j < kCols; ++j) acc.add_rot(j, S[r], C[r], cjt[j], sjt[j]);
                         if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();
                     } else {
                         R v[kCols];
-                        for (int j = 0; j < kCols; ++j)
-                            v[j] = rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j], X0[r], dxt[j])
-                                          : point_direct<F, R>(f, rb, dxt[j], P.h, P.a);
+                        if (rotate) {
+                            for (int j = 0; j < kCols; ++j)
+                                v[j] = point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j], X0[r], dxt[j]);
+                        } else if (fast) {
+                            RowDirect<F, R, true>::eval(f, rb, dcol, P.h, P.a, v);
+                        } else {
+                            RowDirect<F, R, false>::eval(f, rb, dcol, P.h, P.a, v);
+                        }
                         acc.add_row(v);
                     }
                     rb += double(kWidth);
@@ -136,7 +144,8 @@ struct CpuWorker {
                             else
                                 acc.add_one(j, rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j],
                                                                            X0[r], dxt[j])
-                                                      : point_direct<F, R>(f, rb, dxt[j], P.h, P.a));
+                                                      : fast ? point_direct<F, R, true>(f, rb, dxt[j], P.h, P.a)
+                                                             : point_direct<F, R, false>(f, rb, dxt[j], P.h, P.a));
                         }
                 }
                 if (((tile - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || tile + 1 == hi) {

@@ -101,11 +101,7 @@ struct CpuScan {
     Run seg_base[kSegments];
 
     CpuScan(const ScanPlan& P_, const double* table) : P(P_) {
-        Plan fp;
-        memset(&fp, 0, sizeof(fp));
-        for (int i = 0; i < 4; ++i) fp.p[i] = P.p[i];
-        fp.table_len = P.table_len;
-        f = make_functor<F>(fp, table);
+        f = make_scan_functor<F>(P, table);
         agg.assign(2 * P.n_tiles, 0.0);
         prefix.assign(4 * P.n_tiles, 0.0);
     }

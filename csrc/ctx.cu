@@ -226,7 +226,7 @@ static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint3
     Plan* hp = &plan;
     int rc = make_plan(*job, rank, world, c->rows_override, c->table_len, hp);
     if (rc != BQ_OK) return rc;
-    hp->flags = extra_flags | c->fault_flags;
+    hp->flags |= extra_flags | c->fault_flags;
     c->fault_flags = 0;
     hp->timeout_ms = c->timeout_ms;
     if (world > 1 && !(hp->flags & kFlagLocalOnly)) {

@@ -1,5 +1,6 @@
 // Device-side state shared between the host runtime (ctx.cu) and the kernels.
 #pragma once
+#include <stddef.h>
 #include <stdint.h>
 
 #include "bq_dd.cuh"
@@ -7,20 +8,27 @@
 
 namespace bq {
 
-// One per GPU, allocated with cudaMalloc so it can be exported through CUDA IPC
-// and mapped by every peer.  Peers only ever write `slots`, `scan_slots` and
-// add to the two `arrived` counters; `epoch` words are private to the owner.
+// One per GPU, in peer-visible memory (cudaMalloc + CUDA IPC, or a cuMem allocation bound to a
+// multicast object): every peer maps it.  Peers only ever write `ll`, `scan_slots`, `scan_final` and
+// add to the scan counters; the `epoch` words are private to the owner.
+//
+// The partial results cross NVLink as self-validating words ("LL" layout): every 8-byte word
+// carries 32 bits of payload and the 32-bit call number, so one plain store per word is the
+// whole message — no fence, no separate flag, no counter: the reader polls the words themselves
+// and a word whose upper half equals the call number is complete (8-byte stores are
+// single-copy atomic).  A dd pair is 4 such words = one 32-byte store.
 struct alignas(256) CommBlock {
-    uint64_t arrived;         // quad barrier: += 1 per rank per call
+    uint64_t reserved0;       // (was the quad arrival counter)
     uint64_t scan_arrived;    // scan barrier 1 (segment totals published)
     uint64_t scan_done;       // scan barrier 2 (tables + final scalars stored)
     uint64_t epoch;           // calls completed by the owner (quad)
     uint64_t scan_epoch;      // calls completed by the owner (scan)
     uint64_t pad[3];
-    double slots[2][kSegments][2];            // [parity][segment](hi, lo)
+    uint64_t ll[2][kSegments][4];             // [parity][segment]: hi.lo32, hi.hi32, lo.lo32, lo.hi32 | call << 32
     double scan_slots[2][kSegments][4];       // [parity][segment](P_hi, P_lo, Q_hi, Q_lo)
     double scan_final[4];                     // P[n-1], Q[n-1], P[n-2], spare
 };
+static_assert(offsetof(CommBlock, ll) % 32 == 0, "an LL row is one 32-byte run");
 
 struct DeviceState {
     dd* partials;             // [kChunks] chunk sums
@@ -31,6 +39,8 @@ struct DeviceState {
     uint64_t seq;             // call number: written last into the host block (completion word)
     CommBlock* comm;          // own comm block
     CommBlock* peers[BQ_MAX_WORLD];   // comm block of rank r as mapped here
+    CommBlock* mc_comm;       // multicast (NVLS) address of all ranks' comm blocks, or null: one
+                              // multimem.st then reaches every rank's copy through the switch
     const double* table;      // PROFILE table (padded to an even count)
     double* seg_out;          // kFlagLocalOnly: 2*kSegments doubles, else null
     uint64_t* trace;          // optional per-CTA timeline: [cta](start ns, end ns, smid, tiles)

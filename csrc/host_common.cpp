@@ -1,6 +1,8 @@
 // Host-only pieces: plan construction, oracles, the default table, error text.
 #include "host_common.h"
 
+#include "integrands.cuh"
+
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -123,6 +125,13 @@ int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, in
     P->chunk_lo = P->seg_lo * kChunksPerSegment;
     P->chunk_hi = P->seg_hi * kChunksPerSegment;
     P->flags = 0;
+    // DIRECT evaluation of a trig integrand may use the bounded-argument sin/cos when the whole
+    // interval (plus one step of slack for the rule offset) keeps |angle| inside its range.
+    if (trig) {
+        const double w = fabs(P->omega);
+        const double amax = (fabs(job.a) > fabs(job.b) ? fabs(job.a) : fabs(job.b)) + fabs(P->h);
+        if (w * amax <= kFastTrigMax) P->flags |= kFlagFastTrig;
+    }
     P->timeout_ms = 2000;
     return BQ_OK;
 }
@@ -158,6 +167,8 @@ int bq_set_custom_integrand(bq_custom_launch_fn launch, bq_custom_eval_fn eval) 
 const char* bq_last_error(void) { return bq::last_error(); }
 const double* bq_default_profile(int* len) { return bq::default_profile(len); }
 size_t bq_sizeof_params(void) { return sizeof(bq::Plan); }
+double bq_sin_bounded(double x) { return bq::sincos_bounded<false>(x); }
+double bq_cos_bounded(double x) { return bq::sincos_bounded<true>(x); }
 double bq_oracle_sin_sum(double a, double b, uint64_t n, int rule) {
     return (double)bq::oracle_sin_sum(a, b, n, rule);
 }

@@ -28,6 +28,59 @@ BQ_HD double bq_cos(double x) { return cos(x); }
 BQ_HD float bq_sin(float x) { return sinf(x); }
 BQ_HD float bq_cos(float x) { return cosf(x); }
 
+// ---- bounded-argument sine / cosine -------------------------------------------------------
+// libm / libdevice sin() carries a Payne-Hanek path for huge arguments and, on the GPU, costs
+// ~40 fp64-pipe instructions per call.  A definite integral knows its argument range before the
+// first sample is taken (the plan checks |angle| <= kFastTrigMax over [a, b]), so DIRECT
+// evaluation can use this instead: k = rint(x * 2/pi) through the conversion unit (not the fp64
+// pipe), a two-constant Cody-Waite reduction (k * PIO2_HI is exact for |k| < 2^20: PIO2_HI has 33
+// significant bits), and ONE degree-6 polynomial in r^2 whose coefficients are selected by the
+// quadrant (fdlibm's kernel_sin / kernel_cos minimax sets, error < 2^-57 on |r| <= pi/4):
+//     sin(r) = r + (r t)(S1 + S2 t + .. + S6 t^5)      cos(r) = 1 + t(-1/2 + C1 t + .. + C6 t^6)
+// 12 fp64 operations, no branch, identical bits on host and device (same code, explicit fma).
+// Measured against long-double sinl/cosl over |x| <= 1e6: absolute error <= 1.11 * 2^-53, relative
+// < 1.4 ulp away from the zeros (tests/test_cpu_quad.py); next to a zero the error is absolute
+// (|x| * 2^-87), which is what a sum of samples needs.
+constexpr double kFastTrigMax = 1.0e6;
+
+template <bool COS>
+BQ_HD double sincos_bounded(double x) {
+    constexpr double kTwoOverPi = 6.36619772367581382433e-01;
+    constexpr double kPio2Hi = 1.57079632673412561417e+00;     // first 33 bits of pi/2
+    constexpr double kPio2Lo = 6.07710050650619224932e-11;     // pi/2 - kPio2Hi
+    constexpr double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03,
+                     S3 = -1.98412698298579493134e-04, S4 = 2.75573137070700676789e-06,
+                     S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
+    constexpr double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03,
+                     C3 = 2.48015872894767294178e-05, C4 = -2.75573143513906633035e-07,
+                     C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+#if defined(__CUDA_ARCH__)
+    const int k = __double2int_rn(x * kTwoOverPi);
+#else
+    const int k = int(nearbyint(x * kTwoOverPi));               // round-to-nearest-even, as cvt.rni
+#endif
+    const double kd = double(k);
+    double r = fma(-kd, kPio2Hi, x);                            // exact
+    r = fma(-kd, kPio2Lo, r);
+    const int q = k + (COS ? 1 : 0);
+    const bool odd = (q & 1) != 0;
+    const double t = r * r;
+    double p = odd ? C6 : 0.0;
+    p = fma(p, t, odd ? C5 : S6);
+    p = fma(p, t, odd ? C4 : S5);
+    p = fma(p, t, odd ? C3 : S4);
+    p = fma(p, t, odd ? C2 : S3);
+    p = fma(p, t, odd ? C1 : S2);
+    p = fma(p, t, odd ? -0.5 : S1);
+    const double rt = r * t;
+    const double v = fma(odd ? t : rt, p, odd ? 1.0 : r);
+    return (q & 2) ? -v : v;
+}
+BQ_HD double bq_sin_fast(double x) { return sincos_bounded<false>(x); }
+BQ_HD double bq_cos_fast(double x) { return sincos_bounded<true>(x); }
+BQ_HD float bq_sin_fast(float x) { return sinf(x); }
+BQ_HD float bq_cos_fast(float x) { return cosf(x); }
+
 struct SinF {
     static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = false;
     // ROTATE/fp64: the sample sin(x0 + dx) = S*cj + C*sj is added to the running sum by two
@@ -40,6 +93,8 @@ struct SinF {
     BQ_HD double fuse_gamma() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return bq_sin(x); }
+    template <class R>
+    BQ_HD R eval_fast(R x) const { return bq_sin_fast(x); }      // |x| <= kFastTrigMax (checked by the plan)
     BQ_HD double angle(double x) const { return x; }
     template <class R>
     BQ_HD R eval_sc(R, R s, R) const { return s; }
@@ -54,6 +109,8 @@ struct AccF {
     BQ_HD double fuse_gamma() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return -(bq_sin(x / R(tscale)) * R(ascale)); }
+    template <class R>
+    BQ_HD R eval_fast(R x) const { return -(bq_sin_fast(x / R(tscale)) * R(ascale)); }
     BQ_HD double angle(double x) const { return x / tscale; }
     template <class R>
     BQ_HD R eval_sc(R, R s, R) const { return -(s * R(ascale)); }
@@ -68,6 +125,8 @@ struct VelF {
     BQ_HD double fuse_gamma() const { return vscale; }
     template <class R>
     BQ_HD R eval(R x) const { return (-bq_cos(x / R(tscale)) + R(1)) * R(vscale); }
+    template <class R>
+    BQ_HD R eval_fast(R x) const { return (-bq_cos_fast(x / R(tscale)) + R(1)) * R(vscale); }
     BQ_HD double angle(double x) const { return x / tscale; }
     template <class R>
     BQ_HD R eval_sc(R, R, R c) const { return (-c + R(1)) * R(vscale); }
@@ -82,6 +141,8 @@ struct DisF {
     double tscale, vscale;
     template <class R>
     BQ_HD R eval(R x) const { return R(vscale) * bq_fma(-R(tscale), bq_sin(x / R(tscale)), x); }
+    template <class R>
+    BQ_HD R eval_fast(R x) const { return R(vscale) * bq_fma(-R(tscale), bq_sin_fast(x / R(tscale)), x); }
     BQ_HD double angle(double x) const { return x / tscale; }
     template <class R>
     BQ_HD R eval_sc(R x, R s, R) const { return R(vscale) * bq_fma(-R(tscale), s, x); }
@@ -101,6 +162,32 @@ struct ProfileF {
     const double* table;
     int len;
     double inv_dx;
+    double step_du;      // table-index distance between consecutive samples of a run (see eval_run)
+    BQ_HD int cell_of(double u) const {
+        int i = (int)u;
+        return i < 0 ? 0 : (i > len - 2 ? len - 2 : i);
+    }
+    // N samples at x_first + j * step (j = 0..N-1, step = step_du table cells): when the first
+    // and the last one lie in the same cell — a run is short against the table spacing, so
+    // nearly always — the cell index and the slope are worked out once and every sample is ONE
+    // fma, v_j = fma(slope * step_du, j, v_0): the lerp is affine inside a cell.  Otherwise each
+    // sample goes through eval().  x_last is the caller's own x of sample N-1 (same rounding as
+    // eval would see).  Replaces the per-sample table_accel x3 + faccel of 4main.c:249-269.
+    template <int N>
+    BQ_HD bool eval_run(double x_first, double x_last, double (&v)[N]) const {
+        const double u0 = x_first * inv_dx, u1 = x_last * inv_dx;
+        const int i0 = cell_of(u0), i1 = cell_of(u1);
+        if (i0 != i1) return false;
+        const double t0 = table[i0];
+        const double slope = table[i0 + 1] - t0;
+        const double v0 = fma(slope, u0 - double(i0), t0);
+        const double sh = slope * step_du;
+#pragma unroll
+        for (int j = 0; j < N; ++j) v[j] = fma(sh, double(j), v0);
+        return true;
+    }
+    template <class R>
+    BQ_HD R eval_fast(R x) const { return eval(x); }
     template <class R>
     BQ_HD R eval(R x) const {
         // (int)u / R(i): measured on B200, these two conversions are cheaper than any
@@ -131,6 +218,8 @@ struct CustomHostF {
     double p[4];
     template <class R>
     BQ_HD R eval(R x) const { return R(fn(double(x), p)); }
+    template <class R>
+    BQ_HD R eval_fast(R x) const { return eval(x); }
     BQ_HD double angle(double) const { return 0.0; }
     template <class R>
     BQ_HD R eval_sc(R x, R, R) const { return eval(x); }

@@ -42,6 +42,7 @@ constexpr uint64_t kMaxN = 1ull << 40;
 enum PlanFlags : uint32_t {
     kFlagLocalOnly = 1u,     // skip the cross-GPU stage, leave segment pairs in seg_out
     kFlagSkipPublish = 2u,   // fault injection: never publish (peers time out)
+    kFlagFastTrig = 4u,      // DIRECT: |angle| <= kFastTrigMax over [a, b], bounded sin/cos allowed
 };
 
 struct Plan {

@@ -50,6 +50,44 @@ __device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {
     asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(a) : "l"(p) : "memory");
     return a;
 }
+// ---- LL words: 32 bits of payload | 32-bit call number, one 8-byte store each -------------
+__device__ __forceinline__ void st_relaxed_sys_u64x2(uint64_t* p, uint64_t a, uint64_t b) {
+    asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_relaxed_sys_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// NVLS: one store to a multicast address, replicated by the NVSwitch into every bound GPU's memory.
+__device__ __forceinline__ void multimem_st_u64(uint64_t* mc, uint64_t v) {
+    asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_red_add_u64(uint64_t* mc, uint64_t v) {
+    asm volatile("multimem.red.release.sys.global.add.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
+}
+// 4 LL words of a dd pair tagged with `flag` (never 0 for a live call: flag = call number + 1).
+__device__ __forceinline__ void ll_pack(double hi, double lo, uint32_t flag, uint64_t (&w)[4]) {
+    const uint64_t h = uint64_t(__double_as_longlong(hi)), l = uint64_t(__double_as_longlong(lo));
+    const uint64_t f = uint64_t(flag) << 32;
+    w[0] = (h & 0xffffffffull) | f;
+    w[1] = (h >> 32) | f;
+    w[2] = (l & 0xffffffffull) | f;
+    w[3] = (l >> 32) | f;
+}
+__device__ __forceinline__ void ll_store(uint64_t* dst, double hi, double lo, uint32_t flag) {
+    uint64_t w[4];
+    ll_pack(hi, lo, flag, w);
+    st_relaxed_sys_u64x2(dst, w[0], w[1]);
+    st_relaxed_sys_u64x2(dst + 2, w[2], w[3]);
+}
+__device__ __forceinline__ void ll_store_multicast(uint64_t* mc_dst, double hi, double lo, uint32_t flag) {
+    uint64_t w[4];
+    ll_pack(hi, lo, flag, w);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) multimem_st_u64(mc_dst + i, w[i]);
+}
+
 __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 
 // 256-bit global store (sm_100+): one full 32-byte sector per thread.

@@ -38,11 +38,36 @@ BQ_HD R point_rotate(const F& f, R S, R C, R cj, R sj, double x0, double dx) {
 
 // DIRECT: x = a + (i + off) * h with a single rounding (the index arithmetic
 // rowbase + col is exact in fp64 below 2^52), then a plain call of f.
-template <class F, class R>
+// FAST: the plan has verified the argument range of the bounded sin/cos (kFlagFastTrig).
+template <class F, class R, bool FAST = false>
 BQ_HD R point_direct(const F& f, double rowbase, double col, double h, double a) {
     double x = fma(rowbase + col, h, a);
+    if constexpr (FAST) return f.template eval_fast<R>(R(x));
     return f.template eval<R>(R(x));
 }
+
+// DIRECT: the kCols samples of one row of one thread (columns kThreads points apart).
+template <class F, class R, bool FAST>
+struct RowDirect {
+    static BQ_HD void eval(const F& f, double rowbase, const double (&col)[kCols], double h, double a,
+                           R (&v)[kCols]) {
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) v[j] = point_direct<F, R, FAST>(f, rowbase, col[j], h, a);
+    }
+};
+// The table integrand in fp64: the row is a run of equally spaced samples, so when its two ends
+// share a table cell (nearly always) each sample is one fma (ProfileF::eval_run).
+template <bool FAST>
+struct RowDirect<ProfileF, double, FAST> {
+    static BQ_HD void eval(const ProfileF& f, double rowbase, const double (&col)[kCols], double h, double a,
+                           double (&v)[kCols]) {
+        const double x_first = fma(rowbase + col[0], h, a);
+        const double x_last = fma(rowbase + col[kCols - 1], h, a);
+        if (f.template eval_run<kCols>(x_first, x_last, v)) return;
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) v[j] = point_direct<ProfileF, double, false>(f, rowbase, col[j], h, a);
+    }
+};
 
 // Fused accumulation (integrands with kFusedSum, ROTATE, both precisions).  For f = alpha*s + beta*c + gamma
 // with s = S*cj + C*sj, c = C*cj - S*sj the sample is S*P + C*Q + gamma with the per-column
@@ -156,7 +181,9 @@ BQ_HDI AccF make_acc(const Plan& P) { return AccF{P.p[0], P.p[1]}; }
 BQ_HDI VelF make_vel(const Plan& P) { return VelF{P.p[0], P.p[2]}; }
 BQ_HDI DisF make_dis(const Plan& P) { return DisF{P.p[0], P.p[2]}; }
 BQ_HDI ProfileF make_profile(const Plan& P, const double* table) {
-    return ProfileF{table, int(P.table_len), 1.0 / P.p[0]};
+    const double inv_dx = 1.0 / P.p[0];
+    // a row's samples are kThreads points apart (quad kernel); the scan overrides step_du
+    return ProfileF{table, int(P.table_len), inv_dx, double(kThreads) * P.h * inv_dx};
 }
 
 template <class F>
@@ -185,8 +212,9 @@ BQ_HDI void finish_result(const Plan& P, const F& f, const double* seg_hi, const
         acc = dd_add(acc, dd_mul_d(dd{double(P.n), 0.0}, f.fuse_gamma()));   // the constant term of every sample
     dd val = dd_mul_d(acc, P.h);
     if (P.rule == BQ_RULE_TRAP) {
-        double fb = f.template eval<double>(P.b);
-        double fa = f.template eval<double>(P.a);
+        const bool fast = (P.flags & kFlagFastTrig) != 0;   // same sin/cos as the samples: host == device bits
+        double fb = fast ? f.template eval_fast<double>(P.b) : f.template eval<double>(P.b);
+        double fa = fast ? f.template eval_fast<double>(P.a) : f.template eval<double>(P.a);
         val = dd_add_d(val, 0.5 * P.h * (fb - fa));
     }
     out->raw_sum_hi = acc.hi;

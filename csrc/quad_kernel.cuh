@@ -39,6 +39,9 @@
 #ifndef BQ_ROT_UNROLL_F32
 #define BQ_ROT_UNROLL_F32 16    // = kPromoteRows: the promotion lands at the end of an unrolled body
 #endif
+#ifndef BQ_DIRECT_UNROLL
+#define BQ_DIRECT_UNROLL 2      // rows of the DIRECT loop unrolled together (8 independent samples each)
+#endif
 #ifndef BQ_MIN_CTAS
 #define BQ_MIN_CTAS 2
 #endif
@@ -204,6 +207,37 @@ struct PartWorker {
         }
     }
 
+    // `nblk` blocks of kUnroll full rows starting at slot 0: the same pipeline with a body that is
+    // always whole, for any number of full tiles in a flush group (no remainder loop).
+    __device__ __forceinline__ void rows_rotate_blocks(const Vec2<R>* sc_row, const double* x0_row, int nblk,
+                                                       TileAcc<R>& acc) const {
+        constexpr int kUnroll = RotUnroll<R>::value;
+        static_assert(kMaxRows % kUnroll == 0 && kUnroll % kPromoteRows == 0, "a tile is whole blocks");
+        Vec2<R> sc = sc_row[0];
+        double x0 = F::kNeedX ? x0_row[0] : 0.0;
+#pragma unroll 1
+        for (int b = 0; b < nblk; ++b) {
+#pragma unroll
+            for (int r = 0; r < kUnroll; ++r) {
+                const Vec2<R> sc_next = sc_row[b * kUnroll + r + 1];
+                const double x0_next = F::kNeedX ? x0_row[b * kUnroll + r + 1] : 0.0;
+                if constexpr (kFused) {
+#pragma unroll
+                    for (int j = 0; j < kCols; ++j) acc.add_rot(j, sc.x, sc.y, cj[j], sj[j]);
+                    if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();   // fp32 only
+                } else {
+                    R v[kCols];
+#pragma unroll
+                    for (int j = 0; j < kCols; ++j)
+                        v[j] = point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]);
+                    acc.add_row(v);
+                }
+                sc = sc_next;
+                x0 = x0_next;
+            }
+        }
+    }
+
     // ROTATE, any tile (short last tile, tiles of fewer than kMaxRows rows).
     __device__ __forceinline__ void tile_rotate(uint32_t tile, const Vec2<R>* sc_row, const double* x0_row,
                                                 TileAcc<R>& acc) const {
@@ -228,6 +262,7 @@ struct PartWorker {
     }
 
     // DIRECT: adds every sample of `tile` into `acc`.  Only the globally last tile can be short.
+    template <bool FAST>
     __device__ __forceinline__ void tile_direct(uint64_t tile, TileAcc<R>& acc) const {
         TileGeom g;
         if (tile == last_tile) {
@@ -238,11 +273,11 @@ struct PartWorker {
             g.rem = 0;
         }
         double rb = row_base_index(P, g, 0);
-#pragma unroll 2
+        constexpr int kDirectUnroll = BQ_DIRECT_UNROLL;
+#pragma unroll kDirectUnroll
         for (uint32_t r = 0; r < g.full_rows; ++r) {
             R v[kCols];
-#pragma unroll
-            for (int j = 0; j < kCols; ++j) v[j] = point_direct<F, R>(f, rb, dx[j], h, a);
+            RowDirect<F, R, FAST>::eval(f, rb, dx, h, a, v);
             acc.add_row(v);
             rb += double(kWidth);
         }
@@ -250,7 +285,7 @@ struct PartWorker {
 #pragma unroll
             for (int j = 0; j < kCols; ++j)
                 if (threadIdx.x + kThreads * j < g.rem)
-                    acc.add_one(j, point_direct<F, R>(f, rb, dx[j], h, a));
+                    acc.add_one(j, point_direct<F, R, FAST>(f, rb, dx[j], h, a));
         }
     }
 
@@ -280,10 +315,10 @@ struct PartWorker {
                 }
                 const Vec2<R>* sc_row = wSC + buf * kBufStride;
                 const double* x0_row = wX0 + buf * kBufStride;
-                if (nt == uint32_t(kFlushTiles) && rows == uint32_t(kMaxRows) && t + kFlushTiles - 1 < last) {
-                    Vec2<R> sc;
-                    double x0;
-                    rows_rotate<int>(sc_row, x0_row, kGroupRows, acc, sc, x0);
+                if (rows == uint32_t(kMaxRows) && t + nt - 1 < last) {
+                    // every tile of the group is full (also the 1-3 tiles that end a part): one
+                    // software-pipelined loop over all its rows
+                    rows_rotate_blocks(sc_row, x0_row, int(nt) * (kMaxRows / RotUnroll<R>::value), acc);
                 } else {
                     for (uint32_t k = 0; k < nt; ++k)
                         tile_rotate(t + k, sc_row + k * kMaxRows, x0_row + k * kMaxRows, acc);
@@ -294,8 +329,12 @@ struct PartWorker {
                 buf ^= 1;
             }
         } else {
+            const bool fast = F::kTrig && (P.flags & kFlagFastTrig);   // uniform: a kernel parameter
             for (uint64_t t = lo64; t < hi64; ++t) {
-                tile_direct(t, acc);
+                if (fast)
+                    tile_direct<true>(t, acc);
+                else
+                    tile_direct<false>(t, acc);
                 if (((t - lo64) & (kFlushTiles - 1)) == kFlushTiles - 1 || t + 1 == hi64) {
                     total = dd_acc_lazy(total, acc.flush());
                     acc.clear();
@@ -360,6 +399,9 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     const F f = make_functor<F>(P, sTable);
     const Worker worker(P, f, sSC + warp * 2 * Worker::kBufStride,
                         sX0 + (F::kNeedX ? warp * 2 * Worker::kBufStride : 0));
+    // absolute %globaltimer stamps of this CTA (kept by thread 0; only the finishing CTA's are used)
+    uint64_t ts_prologue = 0, ts_tiles = 0;
+    if (tid == 0) ts_prologue = ptx::globaltimer();
 
     const uint32_t cluster_id = blockIdx.x / csize;
     const uint32_t n_clusters = gridDim.x / csize;
@@ -428,6 +470,7 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
                 __syncthreads();
         }
     }
+    if (tid == 0) ts_tiles = ptx::globaltimer();
     if (st.trace && tid == 0) {
         uint32_t smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
@@ -446,6 +489,8 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     __syncthreads();
     if (!sIsLast) return;
     __threadfence();
+    uint64_t ts_ticket = 0, ts_fold = 0, ts_pub = 0, ts_bar = 0;
+    if (tid == 0) ts_ticket = ptx::globaltimer();
     // kernel-entry stamp of CTA 0 (ordered before this point by the ticket chain): fetched now so
     // that the load is long done when the block is assembled
     const uint64_t t_start = *reinterpret_cast<volatile const uint64_t*>(&st.result->t_start_ns);
@@ -477,37 +522,55 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     }
     __syncthreads();
     if (warp != 0) return;
+    if (lane == 0) ts_fold = ts_pub = ts_bar = ptx::globaltimer();
 
     int status = BQ_OK;
+    uint32_t spins = 0;
     const bool exchange = P.world > 1 && !(P.flags & kFlagLocalOnly);
     if (exchange) {
-        // ---- cross-GPU: publish, barrier, gather -----------------------------
+        // ---- cross-GPU: every rank's segment pairs land in every rank's comm block as LL words
+        // (payload | call number per 8-byte word): the stores ARE the message, nothing is fenced
+        // or counted, and the wait below polls the 32 words of this call's parity directly.
         const uint64_t epoch = st.comm->epoch;
         const int par = int(epoch & 1);
-        if (lane < P.world && !(P.flags & kFlagSkipPublish)) {
-            CommBlock* peer = st.peers[lane];
-            for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s)
-                ptx::st_relaxed_sys_f64x2(&peer->slots[par][s][0], sSeg[s].hi, sSeg[s].lo);
-            ptx::red_release_sys_add(&peer->arrived, 1ull);
+        const uint32_t flag = uint32_t(epoch % 0xffffffffull) + 1u;   // never 0 (0 = a cleared block)
+        if (!(P.flags & kFlagSkipPublish)) {
+            if (st.mc_comm) {
+                // NVLS: one multimem.st per word, fanned out by the switch to all ranks (self included)
+                if (uint32_t(lane) < P.seg_hi - P.seg_lo) {
+                    const uint32_t s = P.seg_lo + lane;
+                    ptx::ll_store_multicast(&st.mc_comm->ll[par][s][0], sSeg[s].hi, sSeg[s].lo, flag);
+                }
+            } else if (lane < P.world) {
+                CommBlock* peer = st.peers[lane];
+                for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s)
+                    ptx::ll_store(&peer->ll[par][s][0], sSeg[s].hi, sSeg[s].lo, flag);
+            }
         }
-        __syncwarp();
-        const uint64_t target = uint64_t(P.world) * (epoch + 1);
         const uint64_t t0 = ptx::globaltimer();
+        if (lane == 0) ts_pub = t0;
         const uint64_t limit = uint64_t(P.timeout_ms) * 1000000ull;
-        if (lane == 0) {
-            while (ptx::ld_acquire_sys(&st.comm->arrived) < target) {
-                if (ptx::globaltimer() - t0 > limit) {
+        static_assert(kSegments * 4 == 32, "one LL word per lane");
+        const uint64_t* word = &st.comm->ll[par][0][0] + lane;
+        uint64_t w;
+        for (;;) {
+            w = ptx::ld_relaxed_sys_u64(word);
+            if (__all_sync(0xffffffffu, uint32_t(w >> 32) == flag)) break;
+            if ((++spins & 63u) == 0u) {
+                const bool late = ptx::globaltimer() - t0 > limit;
+                if (__any_sync(0xffffffffu, late)) {
                     status = BQ_ERR_TIMEOUT;
                     break;
                 }
             }
         }
-        status = __shfl_sync(0xffffffffu, status, 0);
-        if (lane < kSegments) {
-            double hi, lo;
-            ptx::ld_relaxed_sys_f64x2(&st.comm->slots[par][lane][0], hi, lo);
-            sSeg[lane] = dd{hi, lo};
-        }
+        if (lane == 0) ts_bar = ptx::globaltimer();
+        // lane s < 8 reassembles segment s from lanes 4s .. 4s+3
+        const uint32_t v = uint32_t(w);
+        const int src = (lane & (kSegments - 1)) * 4;
+        const uint64_t h = uint64_t(__shfl_sync(0xffffffffu, v, src)) | (uint64_t(__shfl_sync(0xffffffffu, v, src + 1)) << 32);
+        const uint64_t l = uint64_t(__shfl_sync(0xffffffffu, v, src + 2)) | (uint64_t(__shfl_sync(0xffffffffu, v, src + 3)) << 32);
+        if (lane < kSegments) sSeg[lane] = dd{__longlong_as_double((long long)h), __longlong_as_double((long long)l)};
         __syncwarp();
         if (lane == 0) st.comm->epoch = epoch + 1;
     }
@@ -529,21 +592,31 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
         sRes.seq = st.seq;
         sRes.reserved = 0;
         *st.ticket = 0u;
-        sRes.t_end_ns = ptx::globaltimer();
+        const uint64_t t_end = ptx::globaltimer();
+        sRes.t_end_ns = t_end;
+        auto rel = [&](uint64_t t) { return t > t_start ? uint32_t(t - t_start) : 0u; };
+        sRes.stamp_ns[BQ_STAMP_PROLOGUE] = rel(ts_prologue);
+        sRes.stamp_ns[BQ_STAMP_TILES] = rel(ts_tiles);
+        sRes.stamp_ns[BQ_STAMP_TICKET] = rel(ts_ticket);
+        sRes.stamp_ns[BQ_STAMP_FOLD] = rel(ts_fold);
+        sRes.stamp_ns[BQ_STAMP_PUBLISHED] = rel(ts_pub);
+        sRes.stamp_ns[BQ_STAMP_BARRIER] = rel(ts_bar);
+        sRes.stamp_ns[BQ_STAMP_RESULT] = rel(t_end);
+        sRes.stamp_ns[BQ_STAMP_SPINS] = spins;
     }
     __syncwarp();
     static_assert(sizeof(bq_result) % 8 == 0 && sizeof(bq_result) / 8 <= 32, "result block = one word per lane");
     constexpr int kWords = int(sizeof(bq_result) / 8);
     constexpr int kSeqWord = int(offsetof(bq_result, seq) / 8);
-    const unsigned long long word = lane < kWords ? reinterpret_cast<const unsigned long long*>(&sRes)[lane] : 0ull;
-    if (lane < kWords) reinterpret_cast<unsigned long long*>(st.result)[lane] = word;
+    const unsigned long long word64 = lane < kWords ? reinterpret_cast<const unsigned long long*>(&sRes)[lane] : 0ull;
+    if (lane < kWords) reinterpret_cast<unsigned long long*>(st.result)[lane] = word64;
     // The device -> host leg of the call: the block goes straight into the context's pinned,
     // mapped host block (a single PCIe write burst) — no copy engine operation follows the
     // kernel.  The call number goes last, after a system-scope fence, so a host that watches
     // that word sees a complete block.
     if (st.result_host) {
         volatile unsigned long long* dst = reinterpret_cast<volatile unsigned long long*>(st.result_host);
-        if (lane < kWords && lane != kSeqWord) dst[lane] = word;
+        if (lane < kWords && lane != kSeqWord) dst[lane] = word64;
         __threadfence_system();
         __syncwarp();
         if (lane == 0) dst[kSeqWord] = st.seq;

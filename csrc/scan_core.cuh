@@ -55,6 +55,28 @@ BQ_HDI int scan_segment_of(const ScanPlan& P, uint64_t tile) {
     return s;
 }
 
+// The integrand functor of a scan: built from the quad plan fields it reads (parameters, table
+// length); for the table integrand the run step is the grid spacing, one sample apart.
+template <class F>
+BQ_HDI F make_scan_functor(const ScanPlan& P, const double* table) {
+    Plan fp{};
+    for (int i = 0; i < 4; ++i) fp.p[i] = P.p[i];
+    fp.table_len = P.table_len;
+    fp.h = P.dx / double(kThreads);   // make_profile: step_du = kThreads * h / spacing = dx / spacing (exact: a power of two)
+    return make_functor<F>(fp, table);
+}
+
+template <class F>
+struct ScanRun {   // the run of kScanItems consecutive samples starting at index `base`; false = not handled
+    static BQ_HD bool eval(const F&, const ScanPlan&, double, double (&)[kScanItems]) { return false; }
+};
+template <>
+struct ScanRun<ProfileF> {
+    static BQ_HD bool eval(const ProfileF& f, const ScanPlan& P, double base, double (&v)[kScanItems]) {
+        return f.template eval_run<kScanItems>(fma(base, P.dx, P.x0), fma(base + double(kScanItems - 1), P.dx, P.x0), v);
+    }
+};
+
 // Thread-level work on its kScanItems consecutive samples of a tile.
 template <class F>
 BQ_HD void scan_thread_values(const F& f, const ScanPlan& P, uint64_t first_idx, uint32_t k0,
@@ -63,6 +85,8 @@ BQ_HD void scan_thread_values(const F& f, const ScanPlan& P, uint64_t first_idx,
     // this is double(first_idx + j) bit for bit.
     const double base = double(first_idx);
     if (k0 + uint32_t(kScanItems) <= m) {
+        // table integrand: cell and slope once per run, one fma per sample (ProfileF::eval_run)
+        if (ScanRun<F>::eval(f, P, base, v)) return;
         // The whole run lies inside the grid (every run but those of the last tile):
         // straight-line code, so the kScanItems evaluations overlap.  A per-sample
         // guard here turns into one branch per sample and serialises them.

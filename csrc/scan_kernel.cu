@@ -175,10 +175,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
         }
         ptx::mbar_wait(&sBar, 0);
     }
-    Plan fp;   // make_functor only reads p[] and table_len
-    for (int i = 0; i < 4; ++i) fp.p[i] = P.p[i];
-    fp.table_len = P.table_len;
-    const F f = make_functor<F>(fp, sTable);
+    const F f = make_scan_functor<F>(P, sTable);
     const uint64_t limit = uint64_t(P.timeout_ms) * 1000000ull;
     const uint64_t gen = sm.gen;
     const bool multi = P.world > 1;

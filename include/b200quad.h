@@ -92,7 +92,22 @@ typedef struct bq_result {
     uint64_t seq;              /* call number of the context; in the host copy of the block it is
                                   the LAST word the kernel writes (completion flag)           */
     uint64_t reserved;
+    /* Where the kernel's fixed per-call time goes: nanoseconds since t_start_ns, taken from
+     * %globaltimer by the CTA that finishes the call (enum bq_stamp).  A stamp the call did not
+     * reach (e.g. no cross-GPU stage in a world of 1) repeats the previous one. */
+    uint32_t stamp_ns[8];
 } bq_result;
+
+enum bq_stamp {
+    BQ_STAMP_PROLOGUE = 0,   /* finishing CTA: column constants / table ready, tile loop starts */
+    BQ_STAMP_TILES = 1,      /* finishing CTA: its last tile summed */
+    BQ_STAMP_TICKET = 2,     /* it drew the last ticket: every chunk sum of this GPU is stored */
+    BQ_STAMP_FOLD = 3,       /* segment sums folded */
+    BQ_STAMP_PUBLISHED = 4,  /* segment pairs stored into every peer (world > 1) */
+    BQ_STAMP_BARRIER = 5,    /* every peer's pairs have arrived */
+    BQ_STAMP_RESULT = 6,     /* result block assembled (== t_end_ns - t_start_ns) */
+    BQ_STAMP_SPINS = 7       /* not a time: polls of the in-kernel barrier loop */
+};
 
 /* ---- cumulative integration (scan) -------------------------------------
  * Capability of 4main.c:76-225: sample f on a uniform grid, running sum
@@ -146,6 +161,12 @@ int bq_cuda_device_count(void);                /* 0 when no driver / no GPU */
 const double* bq_default_profile(int* len);    /* the 1801-entry table */
 /* Bytes moved host->device per call (the parameter block). */
 size_t bq_sizeof_params(void);
+
+/* The bounded-argument sin / cos that DIRECT evaluation uses when the plan has verified
+ * |angle| <= 1e6 over the whole interval (host build of the same code the kernel runs; replaces the
+ * libm sin() call of riemann.cpp:37 / cintegrate.cu:68).  Exposed for the accuracy tests. */
+double bq_sin_bounded(double x);
+double bq_cos_bounded(double x);
 
 /* Closed-form / exactly-rounded oracles used by the tests and the CLIs. */
 double bq_oracle_sin_sum(double a, double b, uint64_t n, int rule);
