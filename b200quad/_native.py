@@ -108,6 +108,7 @@ def _declare(lib, cuda):
     sig("bq_ctx_attach_peers", i32, vp, i32, i32, C.c_char_p)
     sig("bq_ctx_reset_comm", i32, vp)
     sig("bq_ipc_export", i32, vp, C.c_char_p)
+    sig("bq_ipc_export_at", i32, vp, C.c_char_p, P(u64))
     sig("bq_ipc_open", i32, C.c_char_p, P(vp))
     sig("bq_ipc_close", i32, vp)
     sig("bq_ctx_set_scan_peers", i32, vp, P(vp), P(vp))

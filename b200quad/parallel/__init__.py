@@ -233,14 +233,14 @@ class DistWorld:
         lib = self.ctx.lib
         hp = C.create_string_buffer(_native.IPC_HANDLE_BYTES)
         hq = C.create_string_buffer(_native.IPC_HANDLE_BYTES)
-        check(lib.bq_ipc_export(C.c_void_p(tP.data_ptr()), hp), "bq_ipc_export")
-        check(lib.bq_ipc_export(C.c_void_p(tQ.data_ptr()), hq), "bq_ipc_export")
-        # cudaIpc handles address the allocation base: ship the offset too.
-        import torch
-        def base_off(t):
-            return t.data_ptr() - t.untyped_storage().data_ptr()
+        # A cudaIpc handle names the whole cudaMalloc segment; torch's caching allocator hands out
+        # tensors INSIDE segments (two small tables usually share one), so each handle travels with
+        # the tensor's offset from its segment base (cuMemGetAddressRange in bq_ipc_export_at).
+        op_, oq_ = C.c_uint64(), C.c_uint64()
+        check(lib.bq_ipc_export_at(C.c_void_p(tP.data_ptr()), hp, C.byref(op_)), "bq_ipc_export_at")
+        check(lib.bq_ipc_export_at(C.c_void_p(tQ.data_ptr()), hq, C.byref(oq_)), "bq_ipc_export_at")
         gathered = [None] * self.size
-        self.dist.all_gather_object(gathered, (bytes(hp.raw), bytes(hq.raw), base_off(tP), base_off(tQ)),
+        self.dist.all_gather_object(gathered, (bytes(hp.raw), bytes(hq.raw), int(op_.value), int(oq_.value)),
                                     group=self.group)
         aP = (C.c_void_p * _native.MAX_WORLD)()
         aQ = (C.c_void_p * _native.MAX_WORLD)()

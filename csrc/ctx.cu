@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "ctx.h"
+#include "drv.h"
 #include "host_common.h"
 #include "nvtx_range.h"
 #include "quad_launch.h"
@@ -359,6 +360,27 @@ int bq_ipc_export(void* dptr, unsigned char handle[BQ_IPC_HANDLE_BYTES]) {
     BQ_CUDA(cudaIpcGetMemHandle(&h, dptr));
     memcpy(handle, &h, sizeof(h));
     return BQ_OK;
+}
+
+int bq_ipc_export_at(void* dptr, unsigned char handle[BQ_IPC_HANDLE_BYTES], uint64_t* offset) {
+    if (!dptr || !offset) return BQ_ERR_INVALID;
+    // A CUDA-IPC handle names the whole allocation: cudaIpcOpenMemHandle returns the allocation's
+    // base on the importing side, wherever inside it dptr points (a caching allocator hands out
+    // interior pointers), so the exporter ships dptr's offset from that base along with the handle.
+    const drv::Api* d = drv::api();
+    if (!d) {
+        set_error("bq_ipc_export_at: CUDA driver entry points are not available");
+        return BQ_ERR_UNSUPPORTED;
+    }
+    CUdeviceptr base = 0;
+    size_t size = 0;
+    const CUresult r = d->MemGetAddressRange(&base, &size, (CUdeviceptr)(uintptr_t)dptr);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuMemGetAddressRange failed: %s", drv::error_string(r));
+        return BQ_ERR_CUDA;
+    }
+    *offset = uint64_t((uintptr_t)dptr - (uintptr_t)base);
+    return bq_ipc_export(dptr, handle);
 }
 
 int bq_ipc_open(const unsigned char handle[BQ_IPC_HANDLE_BYTES], void** dptr) {

@@ -43,27 +43,63 @@ BQ_HD float bq_cos(float x) { return cosf(x); }
 // (|x| * 2^-87), which is what a sum of samples needs.
 constexpr double kFastTrigMax = 1.0e6;
 
+namespace trig {
+constexpr double kTwoOverPi = 6.36619772367581382433e-01;
+constexpr double kPio2Hi = 1.57079632673412561417e+00;     // first 33 bits of pi/2
+constexpr double kPio2Lo = 6.07710050650619224932e-11;     // pi/2 - kPio2Hi
+constexpr double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03,
+                 S3 = -1.98412698298579493134e-04, S4 = 2.75573137070700676789e-06,
+                 S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
+constexpr double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03,
+                 C3 = 2.48015872894767294178e-05, C4 = -2.75573143513906633035e-07,
+                 C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+}  // namespace trig
+
+// Reduced argument r in [-pi/4, pi/4] and quadrant q (already advanced by one for a cosine):
+// the wanted value is (-1)^(q>>1) * (q odd ? cos r : sin r).
+struct TrigRed {
+    double r;
+    int q;
+};
 template <bool COS>
-BQ_HD double sincos_bounded(double x) {
-    constexpr double kTwoOverPi = 6.36619772367581382433e-01;
-    constexpr double kPio2Hi = 1.57079632673412561417e+00;     // first 33 bits of pi/2
-    constexpr double kPio2Lo = 6.07710050650619224932e-11;     // pi/2 - kPio2Hi
-    constexpr double S1 = -1.66666666666666324348e-01, S2 = 8.33333333332248946124e-03,
-                     S3 = -1.98412698298579493134e-04, S4 = 2.75573137070700676789e-06,
-                     S5 = -2.50507602534068634195e-08, S6 = 1.58969099521155010221e-10;
-    constexpr double C1 = 4.16666666666666019037e-02, C2 = -1.38888888888741095749e-03,
-                     C3 = 2.48015872894767294178e-05, C4 = -2.75573143513906633035e-07,
-                     C5 = 2.08757232129817482790e-09, C6 = -1.13596475577881948265e-11;
+BQ_HD TrigRed trig_reduce(double x) {
 #if defined(__CUDA_ARCH__)
-    const int k = __double2int_rn(x * kTwoOverPi);
+    const int k = __double2int_rn(x * trig::kTwoOverPi);
 #else
-    const int k = int(nearbyint(x * kTwoOverPi));               // round-to-nearest-even, as cvt.rni
+    const int k = int(nearbyint(x * trig::kTwoOverPi));         // round-to-nearest-even, as cvt.rni
 #endif
     const double kd = double(k);
-    double r = fma(-kd, kPio2Hi, x);                            // exact
-    r = fma(-kd, kPio2Lo, r);
-    const int q = k + (COS ? 1 : 0);
-    const bool odd = (q & 1) != 0;
+    double r = fma(-kd, trig::kPio2Hi, x);                      // exact
+    r = fma(-kd, trig::kPio2Lo, r);
+    return TrigRed{r, k + (COS ? 1 : 0)};
+}
+// The three forms below give the same bits for the same (r, parity): the selected form starts the
+// sine's Horner chain with fma(0, t, S6) = S6.  The kernel takes a branch-free unselected form when
+// a whole warp-row has one parity (nearly always: neighbouring samples are a tiny angle apart) and
+// the selected form otherwise; the CPU tree always takes the selected form.
+BQ_HD double trig_poly_sin(double r) {
+    using namespace trig;
+    const double t = r * r;
+    double p = fma(S6, t, S5);
+    p = fma(p, t, S4);
+    p = fma(p, t, S3);
+    p = fma(p, t, S2);
+    p = fma(p, t, S1);
+    return fma(r * t, p, r);
+}
+BQ_HD double trig_poly_cos(double r) {
+    using namespace trig;
+    const double t = r * r;
+    double p = fma(C6, t, C5);
+    p = fma(p, t, C4);
+    p = fma(p, t, C3);
+    p = fma(p, t, C2);
+    p = fma(p, t, C1);
+    p = fma(p, t, -0.5);
+    return fma(t, p, 1.0);
+}
+BQ_HD double trig_poly_sel(double r, bool odd) {
+    using namespace trig;
     const double t = r * r;
     double p = odd ? C6 : 0.0;
     p = fma(p, t, odd ? C5 : S6);
@@ -73,13 +109,23 @@ BQ_HD double sincos_bounded(double x) {
     p = fma(p, t, odd ? C1 : S2);
     p = fma(p, t, odd ? -0.5 : S1);
     const double rt = r * t;
-    const double v = fma(odd ? t : rt, p, odd ? 1.0 : r);
-    return (q & 2) ? -v : v;
+    return fma(odd ? t : rt, p, odd ? 1.0 : r);
 }
-BQ_HD double bq_sin_fast(double x) { return sincos_bounded<false>(x); }
-BQ_HD double bq_cos_fast(double x) { return sincos_bounded<true>(x); }
-BQ_HD float bq_sin_fast(float x) { return sinf(x); }
-BQ_HD float bq_cos_fast(float x) { return cosf(x); }
+BQ_HD double trig_sign(double v, int q) { return (q & 2) ? -v : v; }
+
+template <bool COS>
+BQ_HD double sincos_bounded(double x) {
+    const TrigRed red = trig_reduce<COS>(x);
+    return trig_sign(trig_poly_sel(red.r, (red.q & 1) != 0), red.q);
+}
+// eval_fast of a trig functor in fp64: the bounded sin (or cos) of angle_fast(x) fed to eval_sc —
+// exactly what the row evaluator of the kernel computes (RowDirect, quad_core.cuh), sample by sample.
+template <class F>
+BQ_HD double trig_eval_fast(const F& f, double x) {
+    constexpr bool COS = F::kNeedC;
+    const double sc = sincos_bounded<COS>(f.angle_fast(x));
+    return COS ? f.template eval_sc<double>(x, 0.0, sc) : f.template eval_sc<double>(x, sc, 0.0);
+}
 
 struct SinF {
     static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = false;
@@ -93,9 +139,14 @@ struct SinF {
     BQ_HD double fuse_gamma() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return bq_sin(x); }
+    BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }   // |x| <= kFastTrigMax (plan)
     template <class R>
-    BQ_HD R eval_fast(R x) const { return bq_sin_fast(x); }      // |x| <= kFastTrigMax (checked by the plan)
+    BQ_HD R eval_fast(R x) const {
+        if constexpr (sizeof(R) == 8) return eval_fast_d(x);
+        return eval<R>(x);
+    }
     BQ_HD double angle(double x) const { return x; }
+    BQ_HD double angle_fast(double x) const { return x; }
     template <class R>
     BQ_HD R eval_sc(R, R s, R) const { return s; }
 };
@@ -103,15 +154,20 @@ struct SinF {
 struct AccF {
     static constexpr bool kFusedSum = true;     // -ascale * sin
     static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = false;
-    double tscale, ascale;
+    double tscale, ascale, inv_tscale;
     BQ_HD double fuse_alpha() const { return -ascale; }
     BQ_HD double fuse_beta() const { return 0.0; }
     BQ_HD double fuse_gamma() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return -(bq_sin(x / R(tscale)) * R(ascale)); }
+    BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }
     template <class R>
-    BQ_HD R eval_fast(R x) const { return -(bq_sin_fast(x / R(tscale)) * R(ascale)); }
+    BQ_HD R eval_fast(R x) const {
+        if constexpr (sizeof(R) == 8) return eval_fast_d(x);
+        return eval<R>(x);
+    }
     BQ_HD double angle(double x) const { return x / tscale; }
+    BQ_HD double angle_fast(double x) const { return x * inv_tscale; }   // one multiply instead of a division
     template <class R>
     BQ_HD R eval_sc(R, R s, R) const { return -(s * R(ascale)); }
 };
@@ -119,15 +175,20 @@ struct AccF {
 struct VelF {
     static constexpr bool kFusedSum = true;     // vscale - vscale * cos: the constant is added once, as gamma * n
     static constexpr bool kTrig = true, kNeedS = false, kNeedC = true, kNeedX = false;
-    double tscale, vscale;
+    double tscale, vscale, inv_tscale;
     BQ_HD double fuse_alpha() const { return 0.0; }
     BQ_HD double fuse_beta() const { return -vscale; }
     BQ_HD double fuse_gamma() const { return vscale; }
     template <class R>
     BQ_HD R eval(R x) const { return (-bq_cos(x / R(tscale)) + R(1)) * R(vscale); }
+    BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }
     template <class R>
-    BQ_HD R eval_fast(R x) const { return (-bq_cos_fast(x / R(tscale)) + R(1)) * R(vscale); }
+    BQ_HD R eval_fast(R x) const {
+        if constexpr (sizeof(R) == 8) return eval_fast_d(x);
+        return eval<R>(x);
+    }
     BQ_HD double angle(double x) const { return x / tscale; }
+    BQ_HD double angle_fast(double x) const { return x * inv_tscale; }   // one multiply instead of a division
     template <class R>
     BQ_HD R eval_sc(R, R, R c) const { return (-c + R(1)) * R(vscale); }
 };
@@ -138,12 +199,17 @@ struct DisF {
     BQ_HD double fuse_beta() const { return 0.0; }
     BQ_HD double fuse_gamma() const { return 0.0; }
     static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = true;
-    double tscale, vscale;
+    double tscale, vscale, inv_tscale;
     template <class R>
     BQ_HD R eval(R x) const { return R(vscale) * bq_fma(-R(tscale), bq_sin(x / R(tscale)), x); }
+    BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }
     template <class R>
-    BQ_HD R eval_fast(R x) const { return R(vscale) * bq_fma(-R(tscale), bq_sin_fast(x / R(tscale)), x); }
+    BQ_HD R eval_fast(R x) const {
+        if constexpr (sizeof(R) == 8) return eval_fast_d(x);
+        return eval<R>(x);
+    }
     BQ_HD double angle(double x) const { return x / tscale; }
+    BQ_HD double angle_fast(double x) const { return x * inv_tscale; }   // one multiply instead of a division
     template <class R>
     BQ_HD R eval_sc(R x, R s, R) const { return R(vscale) * bq_fma(-R(tscale), s, x); }
 };

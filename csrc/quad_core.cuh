@@ -55,6 +55,59 @@ struct RowDirect {
         for (int j = 0; j < kCols; ++j) v[j] = point_direct<F, R, FAST>(f, rowbase, col[j], h, a);
     }
 };
+// Trig integrands in fp64 with a verified argument range: bounded reduction per sample, then the
+// polynomial.  On the GPU a warp-row whose 8 x 32 samples all fall in quadrants of one parity
+// (nearly always: neighbouring samples are a tiny angle apart) runs the unselected sine or cosine
+// polynomial — the selected form costs 20 select instructions per sample, more issue slots than
+// its 12 fp64 operations; both forms produce the same bits (integrands.cuh).
+template <class F>
+struct RowDirectTrig {
+    static BQ_HD void eval(const F& f, double rowbase, const double (&col)[kCols], double h, double a,
+                           double (&v)[kCols]) {
+        constexpr bool COS = F::kNeedC;
+        double x[kCols];
+        TrigRed red[kCols];
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) {
+            x[j] = fma(rowbase + col[j], h, a);
+            red[j] = trig_reduce<COS>(f.angle_fast(x[j]));
+        }
+        double val[kCols];
+        bool done = false;
+#if defined(__CUDA_ARCH__)
+        unsigned odd = 0;
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) odd |= unsigned(red[j].q & 1) << j;
+        if (__all_sync(0xffffffffu, odd == 0u)) {
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) val[j] = trig_poly_sin(red[j].r);
+            done = true;
+        } else if (__all_sync(0xffffffffu, odd == (1u << kCols) - 1u)) {
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) val[j] = trig_poly_cos(red[j].r);
+            done = true;
+        }
+#endif
+        if (!done) {
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) val[j] = trig_poly_sel(red[j].r, (red[j].q & 1) != 0);
+        }
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) {
+            const double sc = trig_sign(val[j], red[j].q);
+            v[j] = COS ? f.template eval_sc<double>(x[j], 0.0, sc) : f.template eval_sc<double>(x[j], sc, 0.0);
+        }
+    }
+};
+template <>
+struct RowDirect<SinF, double, true> : RowDirectTrig<SinF> {};
+template <>
+struct RowDirect<AccF, double, true> : RowDirectTrig<AccF> {};
+template <>
+struct RowDirect<VelF, double, true> : RowDirectTrig<VelF> {};
+template <>
+struct RowDirect<DisF, double, true> : RowDirectTrig<DisF> {};
+
 // The table integrand in fp64: the row is a run of equally spaced samples, so when its two ends
 // share a table cell (nearly always) each sample is one fma (ProfileF::eval_run).
 template <bool FAST>
@@ -177,9 +230,9 @@ template <class F>
 struct FunctorOf;
 
 BQ_HDI SinF make_sin(const Plan&) { return SinF{}; }
-BQ_HDI AccF make_acc(const Plan& P) { return AccF{P.p[0], P.p[1]}; }
-BQ_HDI VelF make_vel(const Plan& P) { return VelF{P.p[0], P.p[2]}; }
-BQ_HDI DisF make_dis(const Plan& P) { return DisF{P.p[0], P.p[2]}; }
+BQ_HDI AccF make_acc(const Plan& P) { return AccF{P.p[0], P.p[1], 1.0 / P.p[0]}; }
+BQ_HDI VelF make_vel(const Plan& P) { return VelF{P.p[0], P.p[2], 1.0 / P.p[0]}; }
+BQ_HDI DisF make_dis(const Plan& P) { return DisF{P.p[0], P.p[2], 1.0 / P.p[0]}; }
 BQ_HDI ProfileF make_profile(const Plan& P, const double* table) {
     const double inv_dx = 1.0 / P.p[0];
     // a row's samples are kThreads points apart (quad kernel); the scan overrides step_du

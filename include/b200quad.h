@@ -275,6 +275,10 @@ int bq_ctx_attach_peers(bq_ctx* ctx, int rank, int world,
 int bq_ctx_reset_comm(bq_ctx* ctx);
 /* Same for an output table the scan replicates into (per call buffer). */
 int bq_ipc_export(void* dptr, unsigned char handle[BQ_IPC_HANDLE_BYTES]);
+/* Export of a pointer that may lie INSIDE a larger allocation (e.g. a tensor handed out by a
+ * caching allocator): *offset is dptr's distance from the base of its allocation, which is what
+ * bq_ipc_open returns on the importing side — the peer's view of dptr is base + *offset. */
+int bq_ipc_export_at(void* dptr, unsigned char handle[BQ_IPC_HANDLE_BYTES], uint64_t* offset);
 int bq_ipc_open(const unsigned char handle[BQ_IPC_HANDLE_BYTES], void** dptr);
 int bq_ipc_close(void* dptr);
 int bq_ctx_set_scan_peers(bq_ctx* ctx, double* const* peerP, double* const* peerQ);

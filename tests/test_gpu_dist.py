@@ -14,6 +14,9 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+SMALL_N = (200_000, 123_457)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -36,8 +39,14 @@ def _worker(rank, world, port, n, q):
         vals.append((r.value, r.value_lo, r.status, r.world))
     c = bq.cumulative_integrate(n=3_000_000, dx=6e-4, replicate=True)
     c2 = bq.cumulative_integrate(n=3_000_000, dx=6e-4, replicate=False)
+    # small replicated tables, twice with different n: P and Q of one call share an allocator segment
+    # (and reuse cached blocks on the second call), which is where an IPC offset bug would show
+    small = []
+    for ns in SMALL_N:
+        cs = bq.cumulative_integrate(n=ns, dx=1800.0 / ns, replicate=True)
+        small.append((float(cs.P.sum()), float(cs.Q.sum()), float(cs.P[-1]), float(cs.Q[ns // 2])))
     q.put((rank, vals, c.p_last, c.p_second_last, float(c.P.sum()), float(c.Q[-1]), c2.slice,
-           float(c2.P.sum())))
+           float(c2.P.sum()), small))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -50,6 +59,10 @@ def test_torchrun_layout(world):
     n = (1 << 27) + 3
     one = bq.integrate_result("sin", 0.0, math.pi, n, "left", world=1)
     c1 = bq.cumulative_integrate(n=3_000_000, dx=6e-4, world=1)
+    small1 = []
+    for ns in SMALL_N:
+        cs = bq.cumulative_integrate(n=ns, dx=1800.0 / ns, world=1)
+        small1.append((float(cs.P.sum()), float(cs.Q.sum()), float(cs.P[-1]), float(cs.Q[ns // 2])))
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
@@ -61,7 +74,8 @@ def test_torchrun_layout(world):
         p.join(timeout=120)
         assert p.exitcode == 0
     total_slice = 0.0
-    for rank, vals, p_last, p2, psum, qlast, sl, p2sum in got:
+    for rank, vals, p_last, p2, psum, qlast, sl, p2sum, small in got:
+        assert small == small1
         for v, lo, status, w in vals:
             assert status == 0 and w == world
             assert (v, lo) == (one.value, one.value_lo)
