@@ -78,6 +78,7 @@ def _declare(lib, cuda):
     sig("bq_sin_bounded", dbl, dbl)
     sig("bq_cos_bounded", dbl, dbl)
     sig("bq_set_custom_integrand", i32, vp, vp)
+    sig("bq_register_custom_integrand", i32, vp, vp)
     sig("bq_cpu_integrate", i32, P(Job), i32, P(Result))
     sig("bq_cpu_integrate_segments", i32, P(Job), i32, i32, i32, P(Result))
     sig("bq_fold_segments", i32, P(Job), P(dbl), P(dbl), P(Result))

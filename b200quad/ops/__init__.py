@@ -57,13 +57,14 @@ def make_job(f, a, b, n, rule="left", dtype="fp64", eval="auto", params=None):
     integ, _ = models.get(f)
     if integ is None:
         raise TypeError("make_job needs a library integrand")
-    if integ.native_id == _native.INTEGRANDS["custom"]:
+    native_id = integ.native_id
+    if getattr(integ, "expr", None) is not None:
         from ..models import jit as _custom
-        _custom.activate(integ.expr)        # builds / loads its kernel on first use
+        native_id = _custom.integrand_code(integ.expr)   # builds / loads / registers its kernel on first use
         if params is None:
             params = integ.params
     try:
-        job = Job(integ.native_id, _native.RULES[rule], _native.DTYPES[dtype], _native.EVALS[eval],
+        job = Job(native_id, _native.RULES[rule], _native.DTYPES[dtype], _native.EVALS[eval],
                   float(a), float(b), int(n), (C.c_double * 4)(*(params or (0.0, 0.0, 0.0, 0.0))))
     except KeyError as e:
         raise ValueError("unknown option %s" % e)

@@ -169,7 +169,7 @@ struct CpuWorker {
 
 template <>
 inline CustomHostF make_functor<CustomHostF>(const Plan& P, const double*) {
-    return CustomHostF{custom_eval(), {P.p[0], P.p[1], P.p[2], P.p[3]}};
+    return CustomHostF{custom_eval(P.integrand), {P.p[0], P.p[1], P.p[2], P.p[3]}};
 }
 
 static dd segment_sum(const dd* partials, uint32_t seg) {
@@ -231,14 +231,13 @@ static int cpu_segments(const bq_job* job, int rank, int world, int threads, con
         case BQ_F_VEL: run_f<VelF>(*P, table, threads, hi, lo); break;
         case BQ_F_DIS: run_f<DisF>(*P, table, threads, hi, lo); break;
         case BQ_F_PROFILE: run_f<ProfileF>(*P, table, threads, hi, lo); break;
-        case BQ_F_CUSTOM:
-            if (!custom_eval()) {
+        default:
+            if (P->integrand < BQ_F_CUSTOM || !custom_eval(P->integrand)) {
                 set_error("custom integrand has no host evaluator");
                 return BQ_ERR_INVALID;
             }
             run_f<CustomHostF>(*P, table, threads, hi, lo);
             break;
-        default: return BQ_ERR_INVALID;
     }
     return BQ_OK;
 }
@@ -251,11 +250,10 @@ int fold_segments(const Plan& P, const double* table, const double* hi, const do
         case BQ_F_VEL: finish_result(P, make_functor<VelF>(P, table), hi, lo, out); break;
         case BQ_F_DIS: finish_result(P, make_functor<DisF>(P, table), hi, lo, out); break;
         case BQ_F_PROFILE: finish_result(P, make_functor<ProfileF>(P, table), hi, lo, out); break;
-        case BQ_F_CUSTOM:
-            if (!custom_eval()) return BQ_ERR_INVALID;
+        default:
+            if (P.integrand < BQ_F_CUSTOM || !custom_eval(P.integrand)) return BQ_ERR_INVALID;
             finish_result(P, make_functor<CustomHostF>(P, table), hi, lo, out);
             break;
-        default: return BQ_ERR_INVALID;
     }
     out->status = BQ_OK;
     return BQ_OK;

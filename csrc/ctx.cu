@@ -45,6 +45,9 @@ struct DeviceGuard {
 
 }  // namespace bq
 
+namespace bq {
+static int ctx_init(bq_ctx* c, int device);
+}
 using namespace bq;
 
 extern "C" {
@@ -69,12 +72,29 @@ int bq_ctx_create(int device, bq_ctx** out) {
     DeviceGuard guard(device);
     bq_ctx* c = new bq_ctx();
     c->device = device;
-    cudaDeviceProp prop;
-    BQ_CUDA(cudaGetDeviceProperties(&prop, device));
-    c->sm_count = prop.multiProcessorCount;
+    for (int r = 0; r < BQ_MAX_WORLD; ++r) c->peers[r] = nullptr, c->peer_ipc[r] = false;
+    const int rc = ctx_init(c, device);
+    if (rc != BQ_OK) {
+        bq_ctx_destroy(c);      // frees whatever the failed set-up had already allocated
+        return rc;
+    }
+    *out = c;
+    return BQ_OK;
+}
+
+}  // extern "C"
+
+namespace bq {
+
+// Everything bq_ctx_create allocates; on any failure the caller destroys the half-built context.
+static int ctx_init(bq_ctx* c, int device) {
+    int sms = 0;
+    BQ_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    c->sm_count = sms;
     BQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     BQ_CUDA(cudaEventCreate(&c->ev0));
     BQ_CUDA(cudaEventCreate(&c->ev1));
+    BQ_CUDA(cudaEventCreateWithFlags(&c->ev_order, cudaEventDisableTiming));
 
     BQ_CUDA(cudaMalloc(&c->d_partials, sizeof(dd) * kChunks));
     BQ_CUDA(cudaMemset(c->d_partials, 0, sizeof(dd) * kChunks));
@@ -95,7 +115,6 @@ int bq_ctx_create(int device, bq_ctx** out) {
     BQ_CUDA(cudaHostGetDevicePointer((void**)&c->h_scan_result_dev, c->h_scan_result, 0));
     memset(c->h_result, 0, sizeof(bq_result));
     memset(c->h_scan_result, 0, sizeof(bq_scan_result));
-    for (int r = 0; r < BQ_MAX_WORLD; ++r) c->peers[r] = nullptr, c->peer_ipc[r] = false;
     c->peers[0] = c->d_comm;
 
     int len = 0;
@@ -105,14 +124,17 @@ int bq_ctx_create(int device, bq_ctx** out) {
     rc = scan_ctx_init(c);
     if (rc != BQ_OK) return rc;
     BQ_CUDA(cudaDeviceSynchronize());
-    *out = c;
     return BQ_OK;
 }
+
+}  // namespace bq
+
+extern "C" {
 
 void bq_ctx_destroy(bq_ctx* c) {
     if (!c) return;
     DeviceGuard guard(c->device);
-    cudaStreamSynchronize(c->stream);
+    if (c->stream) cudaStreamSynchronize(c->stream);
     for (int r = 0; r < BQ_MAX_WORLD; ++r)
         if (c->peer_ipc[r] && c->peers[r]) cudaIpcCloseMemHandle(c->peers[r]);
     scan_ctx_free(c);
@@ -125,9 +147,11 @@ void bq_ctx_destroy(bq_ctx* c) {
     cudaFree(c->d_trace);
     cudaFreeHost(c->h_result);
     cudaFreeHost(c->h_scan_result);
-    cudaEventDestroy(c->ev0);
-    cudaEventDestroy(c->ev1);
-    cudaStreamDestroy(c->stream);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev_order) cudaEventDestroy(c->ev_order);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    cudaGetLastError();
     delete c;
 }
 
@@ -205,6 +229,19 @@ int bq_ctx_inject_fault(bq_ctx* c, int kind) {
 
 namespace bq {
 
+int order_after_previous(bq_ctx* c, cudaStream_t stream) {
+    if (!c->last_stream || c->last_stream == stream) return BQ_OK;
+    cudaStreamCaptureStatus a = cudaStreamCaptureStatusNone, b = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &a) != cudaSuccess || cudaStreamIsCapturing(c->last_stream, &b) != cudaSuccess) {
+        cudaGetLastError();       // e.g. the previous stream no longer exists: nothing left to order after
+        return BQ_OK;
+    }
+    if (a != cudaStreamCaptureStatusNone || b != cudaStreamCaptureStatusNone) return BQ_OK;
+    BQ_CUDA(cudaEventRecord(c->ev_order, c->last_stream));
+    BQ_CUDA(cudaStreamWaitEvent(stream, c->ev_order, 0));
+    return BQ_OK;
+}
+
 static LaunchConfig quad_config(const bq_ctx* c, const Plan& P) {
     LaunchConfig cfg;
     cfg.cluster = unsigned(c->cluster);
@@ -253,6 +290,8 @@ static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint3
     st.seg_out = seg_out;
     st.trace = c->d_trace;
     c->trace_ctas = c->d_trace ? int(quad_config(c, *hp).grid) : 0;
+    rc = order_after_previous(c, stream);
+    if (rc != BQ_OK) return rc;
     BQ_CUDA(launch_quad(*hp, st, quad_config(c, *hp), stream));
     c->launches += 1;
     c->last_stream = stream;
@@ -407,6 +446,7 @@ int bq_ctx_attach_peers(bq_ctx* c, int rank, int world, const unsigned char* han
         return BQ_ERR_INVALID;
     }
     DeviceGuard guard(c->device);
+    BQ_CUDA(cudaStreamSynchronize(c->last_stream ? c->last_stream : c->stream));   // no kernel may still use a mapping
     for (int r = 0; r < BQ_MAX_WORLD; ++r) {
         if (c->peer_ipc[r] && c->peers[r]) cudaIpcCloseMemHandle(c->peers[r]);
         c->peers[r] = nullptr;
@@ -503,15 +543,36 @@ bq_ctx* bq_world_ctx(bq_world* w, int rank) {
 int bq_world_integrate(bq_world* w, const bq_job* job, bq_result* out) {
     if (!w || !job) return BQ_ERR_INVALID;
     const int n = int(w->ctx.size());
+    // Everything that can be rejected is checked for EVERY rank before the first launch: a rank
+    // launched alone would sit at the in-kernel barrier until its time-out.
+    for (int r = 0; r < n; ++r) {
+        Plan probe;
+        const int rc = make_plan(*job, r, n, w->ctx[r]->rows_override, w->ctx[r]->table_len, &probe);
+        if (rc != BQ_OK) return rc;
+        for (int q = 0; q < n; ++q)
+            if (!w->ctx[r]->peers[q]) {
+                set_error("rank %d: peer %d is not attached (world=%d)", r, q, n);
+                return BQ_ERR_INVALID;
+            }
+    }
     // Enqueue everywhere first: the kernels meet at the in-kernel barrier, so
     // no rank may be waited for before all have been launched.
     for (int r = 0; r < n; ++r) {
         bq_ctx* c = w->ctx[r];
         DeviceGuard guard(c->device);
-        BQ_CUDA(cudaEventRecord(c->ev0, c->stream));
-        int rc = quad_enqueue(c, job, r, n, 0, nullptr, c->stream);
-        if (rc != BQ_OK) return rc;
-        BQ_CUDA(cudaEventRecord(c->ev1, c->stream));
+        int rc = cudaEventRecord(c->ev0, c->stream) == cudaSuccess ? BQ_OK : BQ_ERR_CUDA;
+        if (rc == BQ_OK) rc = quad_enqueue(c, job, r, n, 0, nullptr, c->stream);
+        if (rc == BQ_OK && cudaEventRecord(c->ev1, c->stream) != cudaSuccess) rc = BQ_ERR_CUDA;
+        if (rc != BQ_OK) {
+            // A launch failed after others went out: let those run into their time-out, then put
+            // every barrier word of the world back to zero so the next call starts clean.
+            for (int q = 0; q < r; ++q) {
+                DeviceGuard g2(w->ctx[q]->device);
+                cudaStreamSynchronize(w->ctx[q]->stream);
+            }
+            for (int q = 0; q < n; ++q) bq_ctx_reset_comm(w->ctx[q]);
+            return rc;
+        }
     }
     int worst = BQ_OK;
     for (int r = 0; r < n; ++r) {

@@ -18,6 +18,7 @@ struct bq_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t last_stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev_order = nullptr;       // orders a launch after the previous one when the stream changes
 
     // launch knobs
     int ctas_per_sm = 2;
@@ -65,4 +66,10 @@ struct bq_ctx {
 namespace bq {
 int scan_ctx_init(bq_ctx* c);
 void scan_ctx_free(bq_ctx* c);
+// One context = one set of scratch (chunk sums, tickets, result blocks, barrier epochs): two of its
+// kernels must never overlap on the GPU.  Calls on one stream are ordered by the stream; when a call
+// arrives on a DIFFERENT stream than the previous one, this makes the new stream wait for everything
+// enqueued so far on the old one (no-op while either stream is being captured: a captured launch is
+// ordered by the graph it ends up in).
+int order_after_previous(bq_ctx* c, cudaStream_t stream);
 }  // namespace bq

@@ -8,6 +8,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
+
 namespace bq {
 
 static const double kDefaultProfile[] = {
@@ -30,11 +32,38 @@ void set_error(const char* fmt, ...) {
 }
 const char* last_error() { return g_err; }
 
-static bq_custom_launch_fn g_custom_launch = nullptr;
-static bq_custom_eval_fn g_custom_eval = nullptr;
-bq_custom_launch_fn custom_launch() { return g_custom_launch; }
-bq_custom_eval_fn custom_eval() { return g_custom_eval; }
-void set_custom(bq_custom_launch_fn l, bq_custom_eval_fn e) { g_custom_launch = l, g_custom_eval = e; }
+// Custom integrands: a table of registered (launch, eval) pairs.  A job names its integrand by
+// code (BQ_F_CUSTOM + slot), so every job carries its own kernel: two threads, or two expressions
+// used alternately, never see each other's entry points.  Slot 0 is the legacy "active" integrand
+// of bq_set_custom_integrand; slots 1.. are write-once.
+struct CustomSlot {
+    bq_custom_launch_fn launch = nullptr;
+    bq_custom_eval_fn eval = nullptr;
+};
+static std::mutex g_custom_mu;
+static CustomSlot g_custom[BQ_MAX_CUSTOM + 1];
+static int g_custom_used = 1;
+
+static CustomSlot custom_slot(int integrand) {
+    const int slot = integrand - BQ_F_CUSTOM;
+    if (slot < 0 || slot > BQ_MAX_CUSTOM) return CustomSlot{};
+    std::lock_guard<std::mutex> lock(g_custom_mu);
+    return slot < g_custom_used ? g_custom[slot] : CustomSlot{};
+}
+bq_custom_launch_fn custom_launch(int integrand) { return custom_slot(integrand).launch; }
+bq_custom_eval_fn custom_eval(int integrand) { return custom_slot(integrand).eval; }
+void set_custom(bq_custom_launch_fn l, bq_custom_eval_fn e) {
+    std::lock_guard<std::mutex> lock(g_custom_mu);
+    g_custom[0].launch = l, g_custom[0].eval = e;
+}
+int register_custom(bq_custom_launch_fn l, bq_custom_eval_fn e) {
+    std::lock_guard<std::mutex> lock(g_custom_mu);
+    for (int i = 1; i < g_custom_used; ++i)
+        if (g_custom[i].launch == l && g_custom[i].eval == e) return BQ_F_CUSTOM + i;   // already known
+    if (g_custom_used > BQ_MAX_CUSTOM) return -1;
+    g_custom[g_custom_used].launch = l, g_custom[g_custom_used].eval = e;
+    return BQ_F_CUSTOM + g_custom_used++;
+}
 
 // n below which AUTO stays with DIRECT evaluation: the ROTATE set-up (three
 // sincos per thread plus one per 32 tiles) has to be paid back.  Measured on B200
@@ -54,7 +83,7 @@ int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, in
         set_error("world=%d rank=%d: world must be 1, 2, 4 or 8", world, rank);
         return BQ_ERR_INVALID;
     }
-    if (job.integrand < 0 || job.integrand >= BQ_F_COUNT || job.rule < 0 || job.rule > BQ_RULE_TRAP ||
+    if (job.integrand < 0 || job.integrand > BQ_F_CUSTOM + BQ_MAX_CUSTOM || job.rule < 0 || job.rule > BQ_RULE_TRAP ||
         job.dtype < 0 || job.dtype > BQ_F32C || job.eval < 0 || job.eval > BQ_EVAL_ROTATE) {
         set_error("bad enum in job (integrand=%d rule=%d dtype=%d eval=%d)", job.integrand, job.rule,
                   job.dtype, job.eval);
@@ -79,8 +108,9 @@ int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, in
     for (int i = 0; i < 4; ++i) P->p[i] = job.p[i];
     const bool trig = job.integrand == BQ_F_SIN || job.integrand == BQ_F_ACC || job.integrand == BQ_F_VEL ||
                       job.integrand == BQ_F_DIS;
-    if (job.integrand == BQ_F_CUSTOM && !custom_eval() && !custom_launch()) {
-        set_error("integrand BQ_F_CUSTOM but no custom integrand is registered (bq_set_custom_integrand)");
+    if (job.integrand >= BQ_F_CUSTOM && !custom_eval(job.integrand) && !custom_launch(job.integrand)) {
+        set_error("integrand code %d: no custom integrand is registered under it "
+                  "(bq_register_custom_integrand / bq_set_custom_integrand)", job.integrand);
         return BQ_ERR_INVALID;
     }
     if (job.integrand == BQ_F_ACC || job.integrand == BQ_F_VEL || job.integrand == BQ_F_DIS) {
@@ -163,6 +193,12 @@ const char* bq_version(void) { return "b200quad 0.1 (sm_100a)"; }
 int bq_set_custom_integrand(bq_custom_launch_fn launch, bq_custom_eval_fn eval) {
     bq::set_custom(launch, eval);
     return BQ_OK;
+}
+int bq_register_custom_integrand(bq_custom_launch_fn launch, bq_custom_eval_fn eval) {
+    if (!launch && !eval) return -1;
+    const int code = bq::register_custom(launch, eval);
+    if (code < 0) bq::set_error("all %d custom integrand slots are in use", BQ_MAX_CUSTOM);
+    return code;
 }
 const char* bq_last_error(void) { return bq::last_error(); }
 const double* bq_default_profile(int* len) { return bq::default_profile(len); }

@@ -61,14 +61,28 @@ struct TrigRed {
     double r;
     int q;
 };
+// BQ_TRIG_MAGIC=1: k through the 1.5 * 2^52 trick (one fma + one add on the fp64 pipe, the integer
+// falls out of the low word) instead of a conversion pair (F2I.F64 + I2F.F64 on the conversion unit).
+#ifndef BQ_TRIG_MAGIC
+#define BQ_TRIG_MAGIC 0
+#endif
 template <bool COS>
 BQ_HD TrigRed trig_reduce(double x) {
+#if BQ_TRIG_MAGIC
+    constexpr double kMagic = 6755399441055744.0;               // 1.5 * 2^52: ulp = 1, so the fma rounds to an integer
+    const double tm = fma(x, trig::kTwoOverPi, kMagic);
+    const double kd = tm - kMagic;
+    long long bits;
+    memcpy(&bits, &tm, sizeof(bits));
+    const int k = int(uint32_t(uint64_t(bits)));                // low 32 bits of the mantissa = k (two's complement)
+#else
 #if defined(__CUDA_ARCH__)
     const int k = __double2int_rn(x * trig::kTwoOverPi);
 #else
     const int k = int(nearbyint(x * trig::kTwoOverPi));         // round-to-nearest-even, as cvt.rni
 #endif
     const double kd = double(k);
+#endif
     double r = fma(-kd, trig::kPio2Hi, x);                      // exact
     r = fma(-kd, trig::kPio2Lo, r);
     return TrigRed{r, k + (COS ? 1 : 0)};

@@ -30,13 +30,13 @@ cudaError_t launch_quad(const Plan& P, const DeviceState& st, const LaunchConfig
         case BQ_F_VEL: return launch_f<VelF>(P, st, cfg, stream);
         case BQ_F_DIS: return launch_f<DisF>(P, st, cfg, stream);
         case BQ_F_PROFILE: return launch_f<ProfileF>(P, st, cfg, stream);
-        case BQ_F_CUSTOM: {
-            // the kernel instantiated for the user's expression lives in its own small library
-            const bq_custom_launch_fn fn = custom_launch();
+        default: {
+            // codes >= BQ_F_CUSTOM: the kernel instantiated for the user's expression lives in its
+            // own small library, found through the job's integrand code
+            const bq_custom_launch_fn fn = P.integrand >= BQ_F_CUSTOM ? custom_launch(P.integrand) : nullptr;
             if (!fn) return cudaErrorInvalidValue;
             return static_cast<cudaError_t>(fn(&P, &st, &cfg, stream));
         }
-        default: return cudaErrorInvalidValue;
     }
 }
 

@@ -20,6 +20,7 @@
 #include <stddef.h>
 #include <stdio.h>
 
+#include <atomic>
 #include <type_traits>
 
 #include "device_state.h"
@@ -401,7 +402,13 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
                         sX0 + (F::kNeedX ? warp * 2 * Worker::kBufStride : 0));
     // absolute %globaltimer stamps of this CTA (kept by thread 0; only the finishing CTA's are used)
     uint64_t ts_prologue = 0, ts_tiles = 0;
-    if (tid == 0) ts_prologue = ptx::globaltimer();
+    // The call number of the cross-GPU exchange is fetched now, by the thread that may need it at
+    // the very end: the L2 miss (~0.7 us) hides behind the tile loop instead of sitting in the tail.
+    uint64_t epoch_pre = 0;
+    if (tid == 0) {
+        ts_prologue = ptx::globaltimer();
+        if (P.world > 1 && !(P.flags & kFlagLocalOnly)) epoch_pre = ptx::ld_relaxed_sys_u64(&st.comm->epoch);
+    }
 
     const uint32_t cluster_id = blockIdx.x / csize;
     const uint32_t n_clusters = gridDim.x / csize;
@@ -531,7 +538,7 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
         // ---- cross-GPU: every rank's segment pairs land in every rank's comm block as LL words
         // (payload | call number per 8-byte word): the stores ARE the message, nothing is fenced
         // or counted, and the wait below polls the 32 words of this call's parity directly.
-        const uint64_t epoch = st.comm->epoch;
+        const uint64_t epoch = __shfl_sync(0xffffffffu, epoch_pre, 0);   // lane 0 of warp 0 is thread 0
         const int par = int(epoch & 1);
         const uint32_t flag = uint32_t(epoch % 0xffffffffull) + 1u;   // never 0 (0 = a cleared block)
         if (!(P.flags & kFlagSkipPublish)) {
@@ -647,15 +654,15 @@ inline cudaError_t launch_one(const Plan& P, const DeviceState& st, const Launch
     if (lc.dynamicSmemBytes > 48 * 1024) {
         // above the default limit (only the double-precision x-dependent trig integrand): opt in,
         // once per device
-        static bool done[64] = {};
+        static std::atomic<bool> done[64];   // zero-initialised; set once per device, any thread
         int dev = 0;
         cudaGetDevice(&dev);
-        if (dev >= 0 && dev < 64 && !done[dev]) {
+        if (dev >= 0 && dev < 64 && !done[dev].load(std::memory_order_acquire)) {
             cudaError_t e = cudaFuncSetAttribute(quad_kernel<F, R, MODE>,
                                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  int(lc.dynamicSmemBytes));
             if (e != cudaSuccess) return e;
-            done[dev] = true;
+            done[dev].store(true, std::memory_order_release);
         }
     }
     cudaLaunchAttribute attr[1];

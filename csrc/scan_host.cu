@@ -127,6 +127,8 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
     uint64_t tiles = hp->tile_hi - hp->tile_lo;
     unsigned grid = unsigned(c->scan_grid);
     if (tiles < grid) grid = unsigned(tiles ? tiles : 1);
+    rc = order_after_previous(c, stream);
+    if (rc != BQ_OK) return rc;
     BQ_CUDA(launch_scan(*hp, st, grid, stream));
     c->launches += 1;
     c->last_stream = stream;

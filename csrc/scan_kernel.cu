@@ -30,6 +30,7 @@
 #include <cuda_runtime.h>
 #include <stdlib.h>
 
+#include <atomic>
 #include <type_traits>
 
 #include "ptx.cuh"
@@ -499,14 +500,14 @@ cudaError_t launch_scan_fr(const ScanPlan& P, const ScanState& st, unsigned grid
     lc.dynamicSmemBytes = REPL ? kScanStageBytes : 0;
     if (REPL) {
         // static table + staging exceeds the default 48 KB for the table integrand: opt in once per device
-        static bool done[64] = {};
+        static std::atomic<bool> done[64];   // zero-initialised; set once per device, any thread
         int dev = 0;
         cudaGetDevice(&dev);
-        if (dev >= 0 && dev < 64 && !done[dev]) {
+        if (dev >= 0 && dev < 64 && !done[dev].load(std::memory_order_acquire)) {
             cudaError_t e = cudaFuncSetAttribute(scan_kernel<F, REPL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  int(kScanStageBytes));
             if (e != cudaSuccess) return e;
-            done[dev] = true;
+            done[dev].store(true, std::memory_order_release);
         }
     }
     cudaLaunchAttribute attr[1];

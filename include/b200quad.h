@@ -26,9 +26,11 @@ enum bq_integrand {
     BQ_F_VEL = 2,
     BQ_F_DIS = 3,
     BQ_F_PROFILE = 4,
-    BQ_F_CUSTOM = 5,   /* user expression compiled into the same fused kernel (see below) */
+    BQ_F_CUSTOM = 5,   /* user expression compiled into the same fused kernel (see below);
+                          codes BQ_F_CUSTOM + 1 .. BQ_F_CUSTOM + BQ_MAX_CUSTOM name registered ones */
     BQ_F_COUNT = 6
 };
+#define BQ_MAX_CUSTOM 64
 
 /* Quadrature rule.  The reference only has LEFT (riemann.cpp:36-39). */
 enum bq_rule { BQ_RULE_LEFT = 0, BQ_RULE_RIGHT = 1, BQ_RULE_MID = 2, BQ_RULE_TRAP = 3 };
@@ -147,10 +149,14 @@ typedef struct bq_scan_result {
  * the library two entry points; jobs with integrand = BQ_F_CUSTOM then use them.
  *   launch(plan, device_state, launch_config, stream) -> cudaError_t as int
  *   eval(x, p[4])                                     -> f(x) on the host (CPU backend, oracles)
- * One custom integrand is active per process at a time. */
+ * bq_register_custom_integrand returns the integrand CODE to put into bq_job.integrand (or -1 when
+ * the BQ_MAX_CUSTOM slots are used up); the pair belongs to the jobs that name it, so any number of
+ * expressions can be in use at once, from any thread.  bq_set_custom_integrand is the older
+ * single-slot form: it (re)binds code BQ_F_CUSTOM itself, process-wide. */
 typedef int (*bq_custom_launch_fn)(const void* plan, const void* device_state, const void* launch_config,
                                    void* stream);
 typedef double (*bq_custom_eval_fn)(double x, const double* p);
+int bq_register_custom_integrand(bq_custom_launch_fn launch, bq_custom_eval_fn eval);
 int bq_set_custom_integrand(bq_custom_launch_fn launch, bq_custom_eval_fn eval);
 
 /* ---- library-level ----------------------------------------------------- */
