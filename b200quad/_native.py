@@ -103,6 +103,7 @@ def _declare(lib, cuda):
     sig("bq_cumulative", i32, vp, P(ScanJob), vp, vp, vp, P(ScanResult))
     sig("bq_cumulative_async", i32, vp, P(ScanJob), vp, vp, vp, vp)
     sig("bq_scan_result_fetch", i32, vp, P(ScanResult))
+    sig("bq_ctx_reserve_scan", i32, vp, u64)
     sig("bq_noalloc_max_samples", u64)
     sig("bq_cumulative_noalloc", i32, i32, P(ScanJob), vp, vp, vp, vp)
     sig("bq_ctx_export_comm", i32, vp, C.c_char_p)
@@ -141,7 +142,8 @@ def load():
         return _lib, _is_cuda
     # B200QUAD_LIB: load another build of the core library (tuning runs compare variants)
     cuda_path = os.environ.get("B200QUAD_LIB") or os.path.join(_LIBDIR, "libb200quad.so")
-    cpu_path = os.path.join(_LIBDIR, "libb200quad_cpu.so")
+    # B200QUAD_CPU_LIB: another build of the CPU library (the sanitizer tier loads its ASan/UBSan build)
+    cpu_path = os.environ.get("B200QUAD_CPU_LIB") or os.path.join(_LIBDIR, "libb200quad_cpu.so")
     if not os.path.exists(cuda_path) and not os.path.exists(cpu_path):
         raise NativeError("native libraries are not built: run `python build.py` "
                           "(or __graft_entry__.build()) in the repository root")

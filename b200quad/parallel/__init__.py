@@ -209,7 +209,10 @@ class DistWorld:
         if device is None:
             device = int(os.environ.get("LOCAL_RANK", self.rank % max(torch.cuda.device_count(), 1)))
         torch.cuda.set_device(device)
-        self.ctx = context(device)
+        # A context of its own: attaching peers turns a context into rank r of a world of N for good
+        # (its kernels then publish into the peers' comm blocks), so the process-wide world-of-1
+        # context that single-GPU calls use (parallel.context()) must stay untouched.
+        self.ctx = Context(device)
         lib = self.ctx.lib
         mine = C.create_string_buffer(_native.IPC_HANDLE_BYTES)
         check(lib.bq_ctx_export_comm(self.ctx.handle, mine), "bq_ctx_export_comm")

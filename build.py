@@ -32,6 +32,8 @@ CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-Wall", "-Wno-u
 
 CUDA_SOURCES = ["quad_kernel.cu", "scan_kernel.cu", "ctx.cu", "scan_host.cu", "noalloc.cu", "drv.cu"]
 HOST_SOURCES = ["host_common.cpp", "cpu_backend.cpp", "cpu_scan.cpp"]
+CPU_ONLY_SOURCES = ["cuda_stubs.cpp"]     # the CUDA entry points as stubs: only in libb200quad_cpu.so
+SAN_FLAGS = ["-fsanitize=address,undefined", "-fno-omit-frame-pointer", "-fno-sanitize-recover=undefined", "-g"]
 
 
 def _run(cmd, log=None):
@@ -94,8 +96,14 @@ def build_core(force=False, verbose=False):
         objs.append(o)
     core = os.path.join(LIBDIR, "libb200quad.so")
     _run([NVCC, "-shared", "-o", core] + objs + host_objs + ["-cudart", "shared"] + ARCH, log)
+    cpu_only_objs = []
+    for src_name in CPU_ONLY_SOURCES:
+        src = os.path.join(CSRC, src_name)
+        o = os.path.join(OBJDIR, src_name + ".o")
+        _compile(src, o, [CXX] + CXX_FLAGS + ["-I" + os.path.join(ROOT, "include")], "cxx", force, log)
+        cpu_only_objs.append(o)
     cpu = os.path.join(LIBDIR, "libb200quad_cpu.so")
-    _run([CXX, "-shared", "-o", cpu] + host_objs + ["-lpthread", "-lm"], log)
+    _run([CXX, "-shared", "-o", cpu] + host_objs + cpu_only_objs + ["-lpthread", "-lm"], log)
     if verbose:
         for cmd, out in log:
             print(cmd)
@@ -151,13 +159,46 @@ def build_cli(force=False):
     return built
 
 
+def build_sanitize():
+    """Host sanitizer tier: the CPU library and the three CLIs built with AddressSanitizer +
+    UndefinedBehaviorSanitizer into build/sanitize/ (tools/sanitize_host.sh runs the CPU test tier
+    and the CLI golden runs under them).  The reference's undefined behaviour — uninitialised
+    accumulators cintegrate.cu:86,135, strlen of an unwritten buffer 4main.c:110, the one-past-the-end
+    table read cintegrate.cu:117 vs :39 — is the class of bug this tier exists to catch."""
+    out_dir = os.path.join(ROOT, "build", "sanitize")
+    os.makedirs(out_dir, exist_ok=True)
+    # the distribution's own g++ knows where its sanitizer runtimes live (a relocated toolchain may not)
+    CXX = os.environ.get("CXX_SANITIZE") or ("/usr/bin/g++" if os.path.exists("/usr/bin/g++") else globals()["CXX"])
+    flags = [f for f in CXX_FLAGS if f != "-O2"] + ["-O1"] + SAN_FLAGS
+    inc = ["-I" + os.path.join(ROOT, "include")]
+    objs = []
+    for src_name in HOST_SOURCES + CPU_ONLY_SOURCES:
+        o = os.path.join(out_dir, src_name + ".o")
+        _run([CXX] + flags + inc + ["-c", os.path.join(CSRC, src_name), "-o", o])
+        objs.append(o)
+    lib = os.path.join(out_dir, "libb200quad_cpu.so")
+    _run([CXX, "-shared", "-o", lib] + objs + SAN_FLAGS + ["-lpthread", "-lm"])
+    built = [lib]
+    for name in ("riemann", "cintegrate", "train4"):
+        exe = os.path.join(out_dir, name)
+        _run([CXX, "-std=c++17", "-O1"] + SAN_FLAGS + inc + [os.path.join(ROOT, "cli", name + ".cpp")] + objs +
+             ["-o", exe, "-lpthread", "-lm"])
+        built.append(exe)
+    return built
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--sanitize", action="store_true", help="build the ASan+UBSan host tier into build/sanitize/")
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--no-torch", action="store_true")
     a = ap.parse_args()
     t0 = time.time()
+    if a.sanitize:
+        print("sanitize:", build_sanitize())
+        print("done in %.1fs" % (time.time() - t0))
+        return
     print("core :", build_core(a.force, a.verbose))
     if not a.no_torch:
         print("torch:", build_torch(a.force))

@@ -67,14 +67,13 @@ inline int parse_eval(const char* v) {
     return parse_enum(v, k, 3, "eval");
 }
 
-// Largest world of 1/2/4/8 that fits the visible GPUs (0 = CPU backend).
-inline int default_world() {
-    const int n = bq_cuda_device_count();
-    if (n >= 8) return 8;
-    if (n >= 4) return 4;
-    if (n >= 2) return 2;
-    return n >= 1 ? 1 : 0;
-}
+// Default world of the zero-argument programs: ONE GPU when there is one (0 = CPU backend).
+// The programs print the reference's wall-clock line, which spans context creation to the result
+// (riemann.cpp:51,91-92; cintegrate.cu:104,139-140): the reference's problem sizes (1e9 intervals,
+// 18e6 samples) are 0.15 ms / 0.06 ms of work on one B200, while every extra GPU adds a context
+// creation and peer wiring (tens of milliseconds each) to that line — the fastest time-to-solution
+// is a world of 1 (measured: profiles/r2/cli_wall.jsonl).  --world 2|4|8 spreads larger problems.
+inline int default_world() { return bq_cuda_device_count() >= 1 ? 1 : 0; }
 
 inline int pick_world(const Args& a) {
     if (!strcmp(a.get("--backend", "auto"), "cpu")) return 0;

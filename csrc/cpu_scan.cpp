@@ -62,6 +62,13 @@ int make_scan_plan(const bq_scan_job& job, int rank, int world, int table_len, S
     P->timeout_ms = 2000;
     P->n_tiles = (job.n + kScanTile - 1) / kScanTile;
     for (int s = 0; s <= kSegments; ++s) P->seg_tile[s] = (uint64_t(s) * P->n_tiles) / kSegments;
+    P->seg_group0[0] = P->seg_super0[0] = 0;
+    for (int s = 0; s < kSegments; ++s) {
+        const uint64_t T = P->seg_tile[s + 1] - P->seg_tile[s];
+        const uint64_t G = (T + kScanGroup - 1) / kScanGroup;
+        P->seg_group0[s + 1] = P->seg_group0[s] + G;
+        P->seg_super0[s + 1] = P->seg_super0[s] + (G + kScanSuper - 1) / kScanSuper;
+    }
     const uint32_t segs = kSegments / world;
     P->seg_lo = rank * segs;
     P->seg_hi = P->seg_lo + segs;
@@ -134,42 +141,55 @@ struct CpuScan {
         return run_from_tile(agg[2 * t], agg[2 * t + 1], double(scan_tile_count(P, t)));
     }
 
+    // Samples covered by tiles [a, b) (only the last tile of the grid is short).
+    double span(uint64_t a, uint64_t b) const { return scan_samples_in_tiles(P, a, b); }
+
+    // The fixed-shape prefix tree of scan_plan.h, segment by segment: what every tile of the kernel
+    // assembles for itself from the aggregates of earlier tiles.
     void segment_prefixes(int seg) {
         const uint64_t t0 = P.seg_tile[seg], t1 = P.seg_tile[seg + 1];
         const uint64_t T = t1 - t0;
-        const uint64_t B = (T + kScanThreads - 1) / kScanThreads;
-        Run mine[kScanThreads];
-        uint64_t lo[kScanThreads], hi[kScanThreads];
-        for (int t = 0; t < kScanThreads; ++t) {
-            lo[t] = t0 + uint64_t(t) * B < t1 ? t0 + uint64_t(t) * B : t1;
-            hi[t] = lo[t] + B < t1 ? lo[t] + B : t1;
-            Run r = run_identity();
-            for (uint64_t i = lo[t]; i < hi[t]; ++i) r = run_combine(r, tile_run(i));
-            mine[t] = r;
-        }
-        Run inc[kScanThreads], warp_tot[kScanThreads / 32];
-        for (int w = 0; w < kScanThreads / 32; ++w) {
-            Run x[32];
-            for (int l = 0; l < 32; ++l) x[l] = mine[w * 32 + l];
-            lanes_inclusive(x, [](const Run& a, const Run& b, int) { return run_combine(a, b); });
-            for (int l = 0; l < 32; ++l) inc[w * 32 + l] = x[l];
-            warp_tot[w] = x[31];
-        }
-        Run last = run_identity();
-        for (int t = 0; t < kScanThreads; ++t) {
-            const int w = t >> 5, l = t & 31;
-            Run excl = l ? inc[t - 1] : run_identity();
-            Run wpre = run_identity();
-            for (int k = 0; k < w; ++k) wpre = run_combine(wpre, warp_tot[k]);
-            Run running = run_combine(wpre, excl);
-            for (uint64_t i = lo[t]; i < hi[t]; ++i) {
-                double* o = &prefix[4 * i];
-                o[0] = running.p.hi, o[1] = running.p.lo, o[2] = running.q.hi, o[3] = running.q.lo;
-                running = run_combine(running, tile_run(i));
+        const uint64_t G = (T + kScanGroup - 1) / kScanGroup;
+        const uint64_t SG = (G + kScanSuper - 1) / kScanSuper;
+        auto combine = [](const Run& a, const Run& b, int) { return run_combine(a, b); };
+        Run sgp = run_identity();                      // SGP(sg-1)
+        for (uint64_t sg = 0; sg < SG; ++sg) {
+            Run gts[kScanSuper];
+            std::vector<Run> aexcl(size_t(kScanSuper) * kScanGroup, run_identity());
+            int gi_last = -1;
+            for (int gi = 0; gi < kScanSuper; ++gi) {
+                gts[gi] = run_identity();
+                const uint64_t g = sg * kScanSuper + gi;
+                if (g >= G) continue;
+                gi_last = gi;
+                Run x[32];
+                int k_last = -1;
+                for (int l = 0; l < 32; ++l) {
+                    const uint64_t j = g * kScanGroup + l;
+                    x[l] = j < T ? tile_run(t0 + j) : run_identity();
+                    if (j < T) k_last = l;
+                }
+                lanes_inclusive(x, combine);
+                for (int l = 0; l < 32; ++l) aexcl[size_t(gi) * kScanGroup + l] = l ? x[l - 1] : run_identity();
+                gts[gi] = x[k_last];                   // GT(g)
             }
-            if (t == kScanThreads - 1) last = running;
+            Run gx[32];
+            for (int gi = 0; gi < 32; ++gi) gx[gi] = gts[gi];
+            lanes_inclusive(gx, combine);              // GTscan(sg)
+            for (int gi = 0; gi <= gi_last; ++gi) {
+                const Run gexcl = gi ? gx[gi - 1] : run_identity();
+                const Run head = run_combine(sgp, gexcl);
+                for (int l = 0; l < 32; ++l) {
+                    const uint64_t j = (sg * kScanSuper + gi) * kScanGroup + l;
+                    if (j >= T) break;
+                    const Run pre = run_combine(head, aexcl[size_t(gi) * kScanGroup + l]);
+                    double* o = &prefix[4 * (t0 + j)];
+                    o[0] = pre.p.hi, o[1] = pre.p.lo, o[2] = pre.q.hi, o[3] = pre.q.lo;
+                }
+            }
+            sgp = run_combine(sgp, gx[gi_last]);       // SGP(sg)
         }
-        seg_tot[seg] = last;
+        seg_tot[seg] = sgp;
     }
 
     void bases() {

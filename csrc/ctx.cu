@@ -475,6 +475,8 @@ int bq_ctx_reset_comm(bq_ctx* c) {
     BQ_CUDA(cudaStreamSynchronize(c->stream));
     BQ_CUDA(cudaMemset(c->d_comm, 0, sizeof(CommBlock)));
     BQ_CUDA(cudaMemset(c->d_ticket, 0, 256));
+    const int rc = scan_clear_scratch(c);
+    if (rc != BQ_OK) return rc;
     BQ_CUDA(cudaDeviceSynchronize());
     return BQ_OK;
 }

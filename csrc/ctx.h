@@ -39,10 +39,9 @@ struct bq_ctx {
     int table_len = 0;
     std::vector<double> h_table;
 
-    // scan scratch (grown on demand, outside the timed path)
-    double* d_scan_agg = nullptr;         // [tiles][2]
-    double* d_scan_prefix = nullptr;      // [tiles][4]
-    double* d_scan_misc = nullptr;        // segment bases, ready flags
+    // scan scratch: LL descriptors (grown on demand, outside the timed path; see scan_launch.h)
+    unsigned char* d_scan_scratch = nullptr;   // tile aggregates | group totals | supergroup prefixes
+    uint64_t* d_scan_misc = nullptr;      // [0..63] segment-base descriptors, [64] abort word
     uint64_t scan_tiles_cap = 0;
     double* scan_peerP[BQ_MAX_WORLD] = {};
     double* scan_peerQ[BQ_MAX_WORLD] = {};
@@ -66,6 +65,7 @@ struct bq_ctx {
 namespace bq {
 int scan_ctx_init(bq_ctx* c);
 void scan_ctx_free(bq_ctx* c);
+int scan_clear_scratch(bq_ctx* c);
 // One context = one set of scratch (chunk sums, tickets, result blocks, barrier epochs): two of its
 // kernels must never overlap on the GPU.  Calls on one stream are ordered by the stream; when a call
 // arrives on a DIFFERENT stream than the previous one, this makes the new stream wait for everything

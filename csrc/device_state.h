@@ -9,8 +9,8 @@
 namespace bq {
 
 // One per GPU, in peer-visible memory (cudaMalloc + CUDA IPC, or a cuMem allocation bound to a
-// multicast object): every peer maps it.  Peers only ever write `ll`, `scan_slots`, `scan_final` and
-// add to the scan counters; the `epoch` words are private to the owner.
+// multicast object): every peer maps it.  Peers only ever write the `*_ll` words; the `epoch` words
+// are private to the owner.
 //
 // The partial results cross NVLink as self-validating words ("LL" layout): every 8-byte word
 // carries 32 bits of payload and the 32-bit call number, so one plain store per word is the
@@ -18,17 +18,15 @@ namespace bq {
 // and a word whose upper half equals the call number is complete (8-byte stores are
 // single-copy atomic).  A dd pair is 4 such words = one 32-byte store.
 struct alignas(256) CommBlock {
-    uint64_t reserved0;       // (was the quad arrival counter)
-    uint64_t scan_arrived;    // scan barrier 1 (segment totals published)
-    uint64_t scan_done;       // scan barrier 2 (tables + final scalars stored)
     uint64_t epoch;           // calls completed by the owner (quad)
-    uint64_t scan_epoch;      // calls completed by the owner (scan)
-    uint64_t pad[3];
-    uint64_t ll[2][kSegments][4];             // [parity][segment]: hi.lo32, hi.hi32, lo.lo32, lo.hi32 | call << 32
-    double scan_slots[2][kSegments][4];       // [parity][segment](P_hi, P_lo, Q_hi, Q_lo)
-    double scan_final[4];                     // P[n-1], Q[n-1], P[n-2], spare
+    uint64_t scan_epoch;      // scan launches completed by the owner = generation of its descriptors
+    uint64_t pad[6];
+    uint64_t ll[2][kSegments][4];             // quad  [parity][segment]: hi.lo32, hi.hi32, lo.lo32, lo.hi32 | call << 32
+    uint64_t scan_ll[2][kSegments][8];        // scan  [parity][segment]: segment total (P_hi, P_lo, Q_hi, Q_lo), 2 words each
+    uint64_t scan_final_ll[2][8];             // scan  [parity]: P[n-1], Q[n-1], P[n-2] (2 words each), 2 spare
+    uint64_t scan_done_ll[2][BQ_MAX_WORLD];   // scan  [parity][rank]: "my stores into your tables are complete" (replicate)
 };
-static_assert(offsetof(CommBlock, ll) % 32 == 0, "an LL row is one 32-byte run");
+static_assert(offsetof(CommBlock, ll) % 32 == 0 && offsetof(CommBlock, scan_ll) % 32 == 0, "LL rows are 16-byte aligned runs");
 
 struct DeviceState {
     dd* partials;             // [kChunks] chunk sums

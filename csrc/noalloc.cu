@@ -9,12 +9,14 @@
 // (bq_cumulative, bq_ctx_create) allocate a context, pinned result blocks and
 // scratch that grows with n; this one allocates nothing, ever.
 //
-// How: the scratch of the fused scan kernel (tile aggregates, tile prefixes,
-// segment bases, tickets, flag words, the result block
-// and a copy of the velocity table) lives in ONE file-scope
-// `static __device__ __align__(256)` array below.  Its size is fixed at build
-// time, which is what bounds n (BQ_NOALLOC_MAX_SAMPLES).  Every GPU that loads
-// this library carries the array (about 1.6 MB) until the process exits.
+// How: the scratch of the fused scan kernel (the descriptors of its tile
+// aggregates, group totals and supergroup prefixes, segment bases, the ticket,
+// the generation word, the result block and a copy of the velocity table) lives
+// in ONE file-scope `static __device__ __align__(256)` array below.  Its size is
+// fixed at build time, which is what bounds n (BQ_NOALLOC_MAX_SAMPLES).  Every
+// GPU that loads this library carries the array (about 1.2 MB) until the process
+// exits.  It always integrates the library's default velocity table: a table set
+// with bq_ctx_set_profile belongs to a context, and this entry point has none.
 //
 // Rules a caller has to know (also in include/b200quad.h):
 //  * The first call on a device performs the one-time set-up for that device:
@@ -26,10 +28,12 @@
 //  * All calls on a device share the one array.  Two calls that overlap on the
 //    GPU (different streams, or the same call issued again before the first
 //    finished on another stream) race on it; serialise them on one stream.
-//  * The array keeps whatever the previous call left.  The words that must
-//    start at zero (tickets, flag/generation words, barrier block, result) are
-//    cleared by a stream-ordered memset at the start of every call; the
-//    aggregate/prefix areas are fully rewritten before they are read.
+//  * The array keeps whatever the previous call left.  What must start at zero
+//    (the ticket, the abort word, the result block) is cleared by a
+//    stream-ordered memset at the start of every call.  The descriptor areas
+//    need no clearing: a descriptor word is valid only when it carries the
+//    generation of the running launch, and the generation word — which the
+//    memset deliberately leaves alone — moves on with every call.
 //  * Single GPU only (a world of 1): peers would need mapped memory.
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -49,19 +53,19 @@ constexpr int kMaxDevices = 64;
 
 // Layout of the static scratch.  `control` is what a call clears up front.
 struct NoAllocControl {
-    CommBlock comm;                   // barrier words + final scalars (world of 1: local only)
     bq_scan_result result;
-    uint64_t ready[2];                // [0] phase A -> B release word, [1] generation done
-    unsigned int ticket_a[8];
-    unsigned int ticket_b[8];
+    uint64_t abort_word;
+    unsigned int ticket[8];
 };
+
+constexpr size_t kNoAllocDescBytes = scan_scratch_layout(kNoAllocMaxTiles).total;
 
 struct NoAllocScratch {
     NoAllocControl control;
-    alignas(32) double segbase[4 * kSegments];
+    CommBlock comm;                               // generation word, segment totals, final scalars (never cleared)
+    alignas(32) uint64_t segbase_ll[8 * kSegments];
     alignas(32) double table[kMaxTable + 2];      // PROFILE table (default ex4vel.h values)
-    alignas(32) double agg[2 * kNoAllocMaxTiles];
-    alignas(32) double prefix[4 * kNoAllocMaxTiles];
+    alignas(256) unsigned char desc[kNoAllocDescBytes];   // tile / group / supergroup descriptors
 };
 
 // The scratch itself.  Host code must never pass this name to a kernel: see set-up below.
@@ -176,15 +180,16 @@ int bq_cumulative_noalloc(int device, const bq_scan_job* job, double* dP, double
 
     ScanState state;
     memset(&state, 0, sizeof(state));
-    state.agg = sc->agg;
-    state.prefix = sc->prefix;
-    state.segbase = sc->segbase;
-    state.ready = sc->control.ready;
-    state.ticket_a = sc->control.ticket_a;
-    state.ticket_b = sc->control.ticket_b;
+    constexpr ScanScratchLayout L = scan_scratch_layout(kNoAllocMaxTiles);
+    state.a_ll = reinterpret_cast<uint64_t*>(sc->desc + L.a_off);
+    state.gt_ll = reinterpret_cast<uint64_t*>(sc->desc + L.gt_off);
+    state.sgp_ll = reinterpret_cast<uint64_t*>(sc->desc + L.sgp_off);
+    state.segbase_ll = sc->segbase_ll;
+    state.abort_word = &sc->control.abort_word;
+    state.ticket = sc->control.ticket;
     state.result = &sc->control.result;
-    state.comm = &sc->control.comm;
-    state.peers[0] = &sc->control.comm;
+    state.comm = &sc->comm;
+    state.peers[0] = &sc->comm;
     state.table = sc->table;
     state.P = dP;
     state.Q = dQ;

@@ -59,6 +59,41 @@ __device__ __forceinline__ uint64_t ld_relaxed_sys_u64(const uint64_t* p) {
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void st_relaxed_gpu_u64x2(uint64_t* p, uint64_t a, uint64_t b) {
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void ld_relaxed_gpu_u64x2(const uint64_t* p, uint64_t& a, uint64_t& b) {
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void ld_relaxed_sys_u64x2(const uint64_t* p, uint64_t& a, uint64_t& b) {
+    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st_release_sys_u64(uint64_t* p, uint64_t v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// One double as two LL words (low half | flag, high half | flag): a 16-byte store.  SYS = the
+// word crosses NVLink (peer memory) or is read by a peer; otherwise it stays inside this GPU.
+template <bool SYS>
+__device__ __forceinline__ void ll_put(uint64_t* dst, double v, uint32_t flag) {
+    const uint64_t b = uint64_t(__double_as_longlong(v)), f = uint64_t(flag) << 32;
+    if (SYS)
+        st_relaxed_sys_u64x2(dst, (b & 0xffffffffull) | f, (b >> 32) | f);
+    else
+        st_relaxed_gpu_u64x2(dst, (b & 0xffffffffull) | f, (b >> 32) | f);
+}
+// True (and v set) when both words carry `flag`.
+template <bool SYS>
+__device__ __forceinline__ bool ll_get(const uint64_t* src, uint32_t flag, double& v) {
+    uint64_t a, b;
+    if (SYS)
+        ld_relaxed_sys_u64x2(src, a, b);
+    else
+        ld_relaxed_gpu_u64x2(src, a, b);
+    if (uint32_t(a >> 32) != flag || uint32_t(b >> 32) != flag) return false;
+    v = __longlong_as_double((long long)((a & 0xffffffffull) | (b << 32)));
+    return true;
+}
+
 // NVLS: one store to a multicast address, replicated by the NVSwitch into every bound GPU's memory.
 __device__ __forceinline__ void multimem_st_u64(uint64_t* mc, uint64_t v) {
     asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");

@@ -49,6 +49,15 @@ BQ_HDI uint32_t scan_tile_count(const ScanPlan& P, uint64_t tile) {
     return left < uint64_t(kScanTile) ? uint32_t(left) : uint32_t(kScanTile);
 }
 
+// Samples covered by tiles [a, b): every tile is full except the last one of the grid.
+BQ_HDI double scan_samples_in_tiles(const ScanPlan& P, uint64_t a, uint64_t b) {
+    if (b <= a) return 0.0;
+    const uint64_t first = a * uint64_t(kScanTile);
+    uint64_t last = b * uint64_t(kScanTile);
+    if (last > P.n) last = P.n;
+    return double(last - first);
+}
+
 BQ_HDI int scan_segment_of(const ScanPlan& P, uint64_t tile) {
     int s = 0;
     for (int k = 1; k < kSegments; ++k) s += (tile >= P.seg_tile[k]) ? 1 : 0;

@@ -34,32 +34,48 @@ struct DevGuard {
 };
 }  // namespace
 
+constexpr size_t kScanMiscWords = 128;   // 64 segment-base words, abort word, spare
+
 int scan_ctx_init(bq_ctx* c) {
-    // misc: [0..31] segment bases (8 x 4 doubles), [32] ready word, [33] generation word
-    BQ_CUDA(cudaMalloc(&c->d_scan_misc, sizeof(double) * 64));
-    BQ_CUDA(cudaMemset(c->d_scan_misc, 0, sizeof(double) * 64));
+    BQ_CUDA(cudaMalloc(&c->d_scan_misc, sizeof(uint64_t) * kScanMiscWords));
+    BQ_CUDA(cudaMemset(c->d_scan_misc, 0, sizeof(uint64_t) * kScanMiscWords));
     c->scan_grid = scan_max_grid(c->device, c->sm_count);
     return BQ_OK;
 }
 
 void scan_ctx_free(bq_ctx* c) {
     cudaFree(c->d_scan_misc);
-    cudaFree(c->d_scan_agg);
-    cudaFree(c->d_scan_prefix);
+    cudaFree(c->d_scan_scratch);
 }
 
-static int scan_reserve(bq_ctx* c, uint64_t tiles) {
+// Descriptor words are valid when they carry the running launch's generation, and generations
+// restart when the comm block is reset: the scratch goes back to zero with it (0 is never valid).
+int scan_clear_scratch(bq_ctx* c) {
+    if (c->d_scan_misc) BQ_CUDA(cudaMemset(c->d_scan_misc, 0, sizeof(uint64_t) * kScanMiscWords));
+    if (c->d_scan_scratch) BQ_CUDA(cudaMemset(c->d_scan_scratch, 0, scan_scratch_layout(c->scan_tiles_cap).total));
+    return BQ_OK;
+}
+
+static int scan_reserve(bq_ctx* c, uint64_t tiles, cudaStream_t stream) {
     if (tiles <= c->scan_tiles_cap) return BQ_OK;
-    // Growing happens outside any timed path (first call of a given size).
-    BQ_CUDA(cudaStreamSynchronize(c->stream));
-    cudaFree(c->d_scan_agg);
-    cudaFree(c->d_scan_prefix);
-    c->d_scan_agg = c->d_scan_prefix = nullptr;
+    // Growing happens outside any timed path (first call of a given size) and never inside a
+    // stream capture: cudaMalloc / cudaFree are not capturable.  bq_ctx_reserve_scan() sizes the
+    // scratch ahead of a capture.
+    cudaStreamCaptureStatus cap_status = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cap_status) == cudaSuccess && cap_status != cudaStreamCaptureStatusNone) {
+        set_error("cumulative: the scan scratch must grow for this n, which cannot happen inside a stream "
+                  "capture; call bq_ctx_reserve_scan(ctx, n) before capturing");
+        return BQ_ERR_INVALID;
+    }
+    BQ_CUDA(cudaStreamSynchronize(c->last_stream ? c->last_stream : c->stream));
+    cudaFree(c->d_scan_scratch);
+    c->d_scan_scratch = nullptr;
     c->scan_tiles_cap = 0;
     uint64_t cap = 16384;
     while (cap < tiles) cap *= 2;
-    BQ_CUDA(cudaMalloc(&c->d_scan_agg, sizeof(double) * 2 * cap));
-    BQ_CUDA(cudaMalloc(&c->d_scan_prefix, sizeof(double) * 4 * cap));
+    const size_t bytes = scan_scratch_layout(cap).total;
+    BQ_CUDA(cudaMalloc(&c->d_scan_scratch, bytes));
+    BQ_CUDA(cudaMemset(c->d_scan_scratch, 0, bytes));
     c->scan_tiles_cap = cap;
     return BQ_OK;
 }
@@ -96,17 +112,18 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
             }
         }
     }
-    rc = scan_reserve(c, hp->tile_hi - hp->tile_lo);
+    rc = scan_reserve(c, hp->tile_hi - hp->tile_lo, stream);
     if (rc != BQ_OK) return rc;
 
     ScanState st;
     memset(&st, 0, sizeof(st));
-    st.agg = c->d_scan_agg;
-    st.prefix = c->d_scan_prefix;
-    st.segbase = c->d_scan_misc;
-    st.ready = reinterpret_cast<uint64_t*>(c->d_scan_misc + 32);
-    st.ticket_a = c->d_ticket + 8;
-    st.ticket_b = c->d_ticket + 16;
+    const ScanScratchLayout L = scan_scratch_layout(c->scan_tiles_cap);
+    st.a_ll = reinterpret_cast<uint64_t*>(c->d_scan_scratch + L.a_off);
+    st.gt_ll = reinterpret_cast<uint64_t*>(c->d_scan_scratch + L.gt_off);
+    st.sgp_ll = reinterpret_cast<uint64_t*>(c->d_scan_scratch + L.sgp_off);
+    st.segbase_ll = c->d_scan_misc;
+    st.abort_word = c->d_scan_misc + 64;
+    st.ticket = c->d_ticket + 16;
     st.result = c->d_scan_result;
     st.result_host = c->h_scan_result_dev;   // the kernel itself writes the result block to the host
     st.comm = c->d_comm;
@@ -148,6 +165,12 @@ int bq_ctx_set_scan_peers(bq_ctx* c, double* const* peerP, double* const* peerQ)
         c->scan_peerQ[r] = peerQ ? peerQ[r] : nullptr;
     }
     return BQ_OK;
+}
+
+int bq_ctx_reserve_scan(bq_ctx* c, uint64_t n) {
+    if (!c || n < 1 || n > kScanMaxN) return BQ_ERR_INVALID;
+    DevGuard guard(c->device);
+    return scan_reserve(c, (n + kScanTile - 1) / kScanTile, c->stream);
 }
 
 int bq_cumulative_async(bq_ctx* c, const bq_scan_job* job, double* dP, double* dQ, double* dS,

@@ -1,32 +1,34 @@
-// The fused cumulative-integration kernel: ONE launch per GPU per call.
+// The fused cumulative-integration kernel: ONE launch per GPU per call, no grid-wide barrier.
 //
 // Reference capability (4main.c:76-225): fill InterpProfile, per-rank running
 // sum, gather to root, serial carry fix-up on the root, MPI_Bcast of 144 MB —
-// twice.  Here, per GPU, in a single persistent launch:
+// twice.  Here every WARP of a persistent grid owns whole tiles (2048 samples) and does, per tile,
 //
-//   phase A   every WARP reduces whole tiles to (sum v, sum of local running
-//             sums); f is evaluated on the fly, no sample array is ever
-//             materialised, and no CTA-wide barrier sits in the tile loop
-//   phase A'  once every tile aggregate is in, one CTA per owned segment turns
-//             that segment's aggregates into exclusive prefixes (fixed-shape
-//             block scan, dd) — the segments in parallel; the last of them
-//             publishes the segment totals into every peer's comm block over
-//             NVLink, meets the peers at an in-kernel barrier and folds the 8
-//             totals in order into segment bases        (replaces 4main.c:134-155)
-//   phase B   every warp re-evaluates its tiles, scans them with the right base
-//             and streams P and Q out in 256-bit stores — into every peer's
-//             table as well when replicate is on (the fused all-gather that
-//             replaces MPI_Bcast, 4main.c:157,221)
-//   end       second in-kernel barrier: when the kernel retires, every rank's
-//             stores into this GPU's tables and the three final scalars are visible
+//   A   evaluate f on the fly (no sample array is ever materialised) and reduce the tile to its
+//       aggregate (sum v, sum of local running sums); publish it as a descriptor
+//   D   "duties" of the last tile of a group / supergroup / segment: fold the aggregates of its
+//       group into the group total, the group totals into the supergroup prefix, and — for the
+//       last tile of a segment — store the segment total into every rank's comm block over
+//       NVLink                                            (replaces 4main.c:134-155, 200-219)
+//   B   read the few descriptors its exclusive prefix is made of (scan_plan.h: <= 31 tile
+//       aggregates, <= 31 group totals, one supergroup prefix, one segment base), re-evaluate
+//       the tile, scan it and stream P and Q out in 256-bit stores — into every peer's table
+//       as well when replicate is on (the fused all-gather that replaces MPI_Bcast,
+//       4main.c:157,221)
 //
-// A tile is 2048 samples = 8 passes of 32 lanes x 8 samples.  The arithmetic
-// tree of a tile (scan_core.cuh) is that of a 256-thread block scan; one warp
-// walks it pass by pass, so the result does not depend on which warp or CTA
-// ran the tile, and matches cpu_scan.cpp bit for bit.
+// A descriptor is a few "LL" words — 32 bits of payload plus the 32-bit generation of the launch
+// per 8-byte word — so publishing is a plain store and waiting is polling the words themselves:
+// no fence, no flag, no counter, nothing to clear between calls.  A tile only ever waits for
+// EARLIER tiles, all of which are held by resident warps (cooperative launch), so the waits end.
 //
-// CTAs of one launch wait on each other, so the grid never exceeds what is
-// co-resident (cooperative launch attribute).
+// One GPU runs A, D, B back to back per tile: a single pass, the evaluation of one tile overlapping
+// the stores of others.  With several GPUs a rank needs the lower ranks' segment totals before
+// its first store, so it runs A + D over all its tiles first and B afterwards; the prefix tree
+// is the same fixed shape either way, so the tables are bit-identical for every world size and
+// match cpu_scan.cpp bit for bit.
+//
+// A tile is 8 passes of 32 lanes x 8 samples.  The arithmetic tree of a tile (scan_core.cuh) is
+// that of a 256-thread block scan; one warp walks it pass by pass.
 #include <cuda_runtime.h>
 #include <stdlib.h>
 
@@ -46,11 +48,8 @@ constexpr int kWarps = kScanThreads / 32;
 constexpr size_t kScanStageBytes = size_t(kWarps) * 2 * 32 * kScanItems * sizeof(double);   // 32 KB
 
 struct ScanSmem {
-    Run warp_tot[kWarps];
-    Run seg_tot[kSegments];
     uint64_t gen;
     int is_last;
-    int status;
 };
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -68,84 +67,96 @@ __device__ __forceinline__ Run shfl_up_run(const Run& r, int d) {
     o.cnt = __shfl_up_sync(0xffffffffu, r.cnt, d);
     return o;
 }
-
-__device__ __forceinline__ bool spin_until(const uint64_t* flag, uint64_t target, bool sys,
-                                           uint64_t limit_ns) {
-    const uint64_t t0 = ptx::globaltimer();
-    for (;;) {
-        const uint64_t v = sys ? ptx::ld_acquire_sys(flag) : ptx::ld_acquire_gpu(flag);
-        if (v >= target) return true;
-        if (ptx::globaltimer() - t0 > limit_ns) return false;
-        __nanosleep(40);
-    }
+__device__ __forceinline__ Run shfl_run(const Run& r, int src) {
+    Run o;
+    o.p.hi = __shfl_sync(0xffffffffu, r.p.hi, src);
+    o.p.lo = __shfl_sync(0xffffffffu, r.p.lo, src);
+    o.q.hi = __shfl_sync(0xffffffffu, r.q.hi, src);
+    o.q.lo = __shfl_sync(0xffffffffu, r.q.lo, src);
+    o.cnt = __shfl_sync(0xffffffffu, r.cnt, src);
+    return o;
 }
-
-// Exclusive scan of the tile aggregates of one segment by the whole CTA:
-// thread t folds a contiguous block of tiles, a Kogge-Stone warp scan and a
-// serial fold over the 8 warp totals stitch the blocks together.
-__device__ void segment_prefixes(const ScanPlan& P, const ScanState& st, int seg, ScanSmem& sm) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint64_t t0 = P.seg_tile[seg], t1 = P.seg_tile[seg + 1];
-    const uint64_t T = t1 - t0;
-    const uint64_t B = (T + kScanThreads - 1) / kScanThreads;
-    const uint64_t lo = t0 + uint64_t(tid) * B < t1 ? t0 + uint64_t(tid) * B : t1;
-    const uint64_t hi = lo + B < t1 ? lo + B : t1;
-
-    // Both sequential folds below read their tile aggregates in batches: the loads
-    // of a batch are all in flight before the first dependent dd combine, instead
-    // of one L2 round trip per tile on the critical path.
-    constexpr int kBatch = 8;
-    Run mine = run_identity();
-    for (uint64_t t = lo; t < hi; t += kBatch) {
-        double s[kBatch], w[kBatch];
-#pragma unroll
-        for (int k = 0; k < kBatch; ++k) {
-            const uint64_t tt = t + k < hi ? t + k : hi - 1;
-            const double* a = st.agg + 2 * (tt - P.tile_lo);
-            s[k] = __ldcg(a), w[k] = __ldcg(a + 1);
-        }
-#pragma unroll
-        for (int k = 0; k < kBatch; ++k)
-            if (t + k < hi) mine = run_combine(mine, run_from_tile(s[k], w[k], double(scan_tile_count(P, t + k))));
-    }
-    Run inc = mine;
+// Kogge-Stone inclusive scan over the lanes (lanes_inclusive() of cpu_scan.cpp).
+__device__ __forceinline__ Run lanes_inclusive(Run inc) {
+    const int lane = threadIdx.x & 31;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const Run up = shfl_up_run(inc, d);
         if (lane >= d) inc = run_combine(up, inc);
     }
-    if (lane == 31) sm.warp_tot[warp] = inc;
-    __syncthreads();
-    Run excl = shfl_up_run(inc, 1);
-    if (lane == 0) excl = run_identity();
-    Run wpre = run_identity();
-    for (int w = 0; w < warp; ++w) wpre = run_combine(wpre, sm.warp_tot[w]);
-    Run running = run_combine(wpre, excl);
-    for (uint64_t t = lo; t < hi; t += kBatch) {
-        double s[kBatch], w[kBatch];
-#pragma unroll
-        for (int k = 0; k < kBatch; ++k) {
-            const uint64_t tt = t + k < hi ? t + k : hi - 1;
-            const double* a = st.agg + 2 * (tt - P.tile_lo);
-            s[k] = __ldcg(a), w[k] = __ldcg(a + 1);
-        }
-#pragma unroll
-        for (int k = 0; k < kBatch; ++k) {
-            if (t + k < hi) {
-                double* o = st.prefix + 4 * (t + k - P.tile_lo);
-                ptx::st_f64x4(o, running.p.hi, running.p.lo, running.q.hi, running.q.lo);
-                running = run_combine(running, run_from_tile(s[k], w[k], double(scan_tile_count(P, t + k))));
-            }
-        }
-    }
-    if (tid == kScanThreads - 1) sm.seg_tot[seg] = running;
-    __syncthreads();
+    return inc;
 }
+
+// A (dd P, dd Q) pair as 8 LL words.
+template <bool SYS>
+__device__ __forceinline__ void run_put(uint64_t* dst, const Run& r, uint32_t flag) {
+    ptx::ll_put<SYS>(dst + 0, r.p.hi, flag);
+    ptx::ll_put<SYS>(dst + 2, r.p.lo, flag);
+    ptx::ll_put<SYS>(dst + 4, r.q.hi, flag);
+    ptx::ll_put<SYS>(dst + 6, r.q.lo, flag);
+}
+template <bool SYS>
+__device__ __forceinline__ bool run_get(const uint64_t* src, uint32_t flag, Run& r) {
+    double a, b, c, d;
+    const bool ok = ptx::ll_get<SYS>(src + 0, flag, a) & ptx::ll_get<SYS>(src + 2, flag, b) &
+                    ptx::ll_get<SYS>(src + 4, flag, c) & ptx::ll_get<SYS>(src + 6, flag, d);
+    if (ok) r.p = dd{a, b}, r.q = dd{c, d};
+    return ok;
+}
+
+// Warp-collective end-of-wait test for the polling loops: done when every lane has what it needs,
+// or when this warp (or any other: abort word) has waited longer than the time-out.
+struct Waiter {
+    const uint64_t* abort_word;
+    uint64_t* abort_word_w;
+    uint64_t gen, limit_ns, t0;
+    uint32_t spins;
+    bool failed;
+    __device__ __forceinline__ Waiter(uint64_t* aw, uint64_t g, uint64_t limit)
+        : abort_word(aw), abort_word_w(aw), gen(g), limit_ns(limit), t0(0), spins(0), failed(false) {}
+    __device__ __forceinline__ bool done(bool ok) {
+        if (__all_sync(0xffffffffu, ok)) return true;
+        if ((++spins & 31u) == 0u) {
+            if (!t0) t0 = ptx::globaltimer();
+            const bool late = ptx::globaltimer() - t0 > limit_ns;
+            const bool aborted = ptx::ld_acquire_gpu(abort_word) == gen;
+            if (__any_sync(0xffffffffu, late || aborted)) {
+                if ((threadIdx.x & 31) == 0) ptx::st_release_gpu(abort_word_w, gen);
+                failed = true;
+                return true;
+            }
+            __nanosleep(64);
+        }
+        return false;
+    }
+    __device__ __forceinline__ void rearm() { t0 = 0, spins = 0; }
+};
 
 struct ScanParams {
     ScanPlan P;        // rides in the kernel parameter buffer
     ScanState st;
 };
+
+// Where tile `tile` sits in the prefix tree of its segment.
+struct TilePos {
+    int seg;
+    uint64_t j, T;          // index inside the segment, tiles of the segment
+    int k, gi;              // index inside the group, of the group inside its supergroup
+    uint64_t g, sg;         // group / supergroup index inside the segment
+    bool last_in_seg;
+};
+__device__ __forceinline__ TilePos tile_pos(const ScanPlan& P, uint64_t tile) {
+    TilePos t;
+    t.seg = scan_segment_of(P, tile);
+    t.j = tile - P.seg_tile[t.seg];
+    t.T = P.seg_tile[t.seg + 1] - P.seg_tile[t.seg];
+    t.g = t.j / kScanGroup;
+    t.k = int(t.j % kScanGroup);
+    t.sg = t.g / kScanSuper;
+    t.gi = int(t.g % kScanSuper);
+    t.last_in_seg = t.j + 1 == t.T;
+    return t;
+}
 
 // Two resident CTAs per SM (128 registers): measured best on B200 — the register room lets
 // the compiler overlap the passes of a tile; 3 and 4 CTAs/SM (80 / 64 registers) both lost.
@@ -163,8 +174,9 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (blockIdx.x == 0 && tid == 0) st.result->t_start_ns = ptx::globaltimer();
     if (tid == 0) {
-        sm.gen = ptx::ld_acquire_gpu(st.ready + 1) + 1;   // generation of this launch
-        sm.status = BQ_OK;
+        // generation of this launch: one more than the number of scans this context has completed
+        // (written by the last CTA of the previous launch, ordered by the stream)
+        sm.gen = st.comm->scan_epoch + 1;
         if (kIsProfile) ptx::mbar_init(&sBar, 1);
     }
     __syncthreads();
@@ -179,12 +191,25 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
     const F f = make_scan_functor<F>(P, sTable);
     const uint64_t limit = uint64_t(P.timeout_ms) * 1000000ull;
     const uint64_t gen = sm.gen;
+    const uint32_t flag = uint32_t(gen % 0xffffffffull) + 1u;     // never 0
+    const int par = int(gen & 1);
     const bool multi = P.world > 1;
     const uint64_t gwarp = uint64_t(blockIdx.x) * kWarps + warp;
     const uint64_t nwarps = uint64_t(gridDim.x) * kWarps;
+    const bool replicate = REPL && multi && (P.flags & kScanReplicate);
+    extern __shared__ __align__(32) double sStage[];   // replicate only: [warp][P 256 | Q 256]
+    double* const stage = sStage + warp * (2 * 32 * kScanItems);
+    Waiter wait(st.abort_word, gen, limit);
 
-    // ---- phase A: tile aggregates, one warp per tile ---------------------------
-    for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
+    // Totals of owned segments that hold no tile (tiny n): nobody's duty, published up front.
+    if (gwarp == 0 && lane < P.world && !(P.flags & kScanSkipPublish)) {
+        for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s)
+            if (P.seg_tile[s + 1] == P.seg_tile[s])
+                run_put<true>(&st.peers[lane]->scan_ll[par][s][0], run_identity(), flag);
+    }
+
+    // ---- A + duties of one tile ------------------------------------------------------------
+    auto do_a = [&](uint64_t tile) {
         const uint32_t m = scan_tile_count(P, tile);
         // pass j = the samples of "warp j" of a block scan; each lane folds its 8 pass
         // shares in the order ((0+4)+(2+6)) + ((1+5)+(3+7)), the 32 lanes then meet in
@@ -211,128 +236,118 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
         sc += sd, wc += wd;
         // the lane's 8 pass shares are folded first, then ONE butterfly per tile
         const double S = warp_sum(sa + sc), W = warp_sum(wa + wc);
-        if (lane == 0) ptx::st_f64x2(st.agg + 2 * (tile - P.tile_lo), S, W);
-    }
-    __syncthreads();
-    if (tid == 0) {
-        __threadfence();
-        atomicAdd(st.ticket_a, 1u);
-    }
+        uint64_t* mine = st.a_ll + 4 * (tile - P.tile_lo);
+        if (lane == 0) {
+            ptx::ll_put<false>(mine + 0, S, flag);
+            ptx::ll_put<false>(mine + 2, W, flag);
+        }
+        const TilePos tp = tile_pos(P, tile);
+        if (tp.k != kScanGroup - 1 && !tp.last_in_seg) return;
 
-    // ---- phase A': prefixes (segments in parallel), exchange, segment bases -----
-    const uint32_t owned = P.seg_hi - P.seg_lo;
-    const uint32_t workers = owned < gridDim.x ? owned : gridDim.x;
-    if (blockIdx.x < workers) {
-        if (tid == 0) {
-            const uint64_t t0 = ptx::globaltimer();
-            while (ptx::ld_acquire_gpu_u32(st.ticket_a) < gridDim.x) {
-                if (ptx::globaltimer() - t0 > 4 * limit) {
-                    sm.status = BQ_ERR_TIMEOUT;
-                    break;
-                }
+        // -- group duty: GT(g) = last element of the inclusive scan over the group's aggregates
+        Run r = run_identity();
+        {
+            double s = 0.0, w = 0.0;
+            bool ok = lane >= tp.k;
+            const uint64_t* src = mine - 4 * (tp.k - lane);     // tile - k + lane
+            wait.rearm();
+            for (;;) {
+                if (!ok) ok = ptx::ll_get<false>(src, flag, s) && ptx::ll_get<false>(src + 2, flag, w);
+                if (wait.done(ok)) break;
             }
+            if (lane < tp.k) r = run_from_tile(s, w, double(kScanTile));     // predecessors are full tiles
+            if (lane == tp.k) r = run_from_tile(S, W, double(m));
         }
-        if (tid < kSegments) sm.seg_tot[tid] = run_identity();
-        __syncthreads();
-        __threadfence();
-        for (uint32_t s = P.seg_lo + blockIdx.x; s < P.seg_hi; s += workers) {
-            segment_prefixes(P, st, int(s), sm);
-            if (tid == 0) {
-                // This segment's total goes where a peer would publish it: the slot of
-                // this call's parity in the own comm block, for the CTA that folds the bases.
-                const Run r = sm.seg_tot[s];
-                double* o = &st.comm->scan_slots[int(st.comm->scan_epoch & 1)][s][0];
-                ptx::st_relaxed_sys_f64x2(o, r.p.hi, r.p.lo);
-                ptx::st_relaxed_sys_f64x2(o + 2, r.q.hi, r.q.lo);
-            }
-        }
-        __syncthreads();
-        if (tid == 0) {
-            __threadfence();
-            sm.is_last = (atomicAdd(st.ticket_a + 1, 1u) == workers - 1);
-        }
-        __syncthreads();
-        if (sm.is_last && warp == 0) {
-            __threadfence();
-            int status = sm.status;
-            if (lane == 0) st.result->reserved[0] = ptx::globaltimer();   // all prefixes done
-            if (lane < kSegments) {
-                Run r = run_identity();
-                if (uint32_t(lane) >= P.seg_lo && uint32_t(lane) < P.seg_hi) {
-                    const double* o = &st.comm->scan_slots[int(st.comm->scan_epoch & 1)][lane][0];
-                    ptx::ld_relaxed_sys_f64x2(o, r.p.hi, r.p.lo);
-                    ptx::ld_relaxed_sys_f64x2(o + 2, r.q.hi, r.q.lo);
-                }
-                sm.seg_tot[lane] = r;
-            }
-            __syncwarp();
-            if (multi) {
-                const uint64_t epoch = st.comm->scan_epoch;
-                const int par = int(epoch & 1);
-                if (lane < P.world && !(P.flags & kScanSkipPublish)) {
-                    CommBlock* peer = st.peers[lane];
-                    for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s) {
-                        const Run r = sm.seg_tot[s];
-                        ptx::st_relaxed_sys_f64x2(&peer->scan_slots[par][s][0], r.p.hi, r.p.lo);
-                        ptx::st_relaxed_sys_f64x2(&peer->scan_slots[par][s][2], r.q.hi, r.q.lo);
-                    }
-                    ptx::red_release_sys_add(&peer->scan_arrived, 1ull);
-                }
-                __syncwarp();
-                if (lane == 0 &&
-                    !spin_until(&st.comm->scan_arrived, uint64_t(P.world) * (epoch + 1), true, limit))
-                    status = BQ_ERR_TIMEOUT;
-                status = __shfl_sync(0xffffffffu, status, 0);
-                if (lane < kSegments) {
-                    Run r;
-                    ptx::ld_relaxed_sys_f64x2(&st.comm->scan_slots[par][lane][0], r.p.hi, r.p.lo);
-                    ptx::ld_relaxed_sys_f64x2(&st.comm->scan_slots[par][lane][2], r.q.hi, r.q.lo);
-                    r.cnt = 0.0;
-                    sm.seg_tot[lane] = r;
-                }
-                __syncwarp();
-            }
-            if (lane == 0) {
-                Run base = run_identity();
-                for (int s = 0; s < kSegments; ++s) {
-                    double* o = st.segbase + 4 * s;
-                    o[0] = base.p.hi, o[1] = base.p.lo, o[2] = base.q.hi, o[3] = base.q.lo;
-                    Run t = sm.seg_tot[s];
-                    const uint64_t first = P.seg_tile[s] * uint64_t(kScanTile);
-                    uint64_t last = P.seg_tile[s + 1] * uint64_t(kScanTile);
-                    if (last > P.n) last = P.n;
-                    t.cnt = double(last - first);
-                    base = run_combine(base, t);
-                }
-                st.result->status = status;
-                st.ticket_a[0] = 0u;
-                st.ticket_a[1] = 0u;
-                st.result->reserved[1] = ptx::globaltimer();                // bases ready
-                __threadfence();
-                ptx::st_release_gpu(st.ready, gen);
-            }
-        }
-    }
-    if (tid == 0) {
-        if (!spin_until(st.ready, gen, false, 4 * limit)) sm.status = BQ_ERR_TIMEOUT;
-    }
-    __syncthreads();
+        const Run gt = shfl_run(lanes_inclusive(r), tp.k);
+        const uint64_t gidx = P.seg_group0[tp.seg] - P.seg_group0[P.seg_lo] + tp.g;
+        if (lane == 0) run_put<false>(st.gt_ll + 8 * gidx, gt, flag);
+        if (tp.gi != kScanSuper - 1 && !tp.last_in_seg) return;
 
-    // ---- phase B: scan + store, one warp per tile --------------------------------
-    const bool replicate = REPL && multi && (P.flags & kScanReplicate);
-    extern __shared__ __align__(32) double sStage[];   // replicate only: [warp][P 256 | Q 256]
-    double* const stage = sStage + warp * (2 * 32 * kScanItems);
-    for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
+        // -- supergroup duty: SGP(sg) = SGP(sg-1) (+) last element of the scan over its group totals
+        Run q = run_identity();
+        {
+            Run got = run_identity();
+            bool ok = lane >= tp.gi;
+            const uint64_t* src = st.gt_ll + 8 * (gidx - tp.gi + lane);
+            wait.rearm();
+            for (;;) {
+                if (!ok) ok = run_get<false>(src, flag, got);
+                if (wait.done(ok)) break;
+            }
+            if (lane < tp.gi) q = got, q.cnt = double(kScanGroup) * double(kScanTile);   // predecessors are full groups
+            if (lane == tp.gi) q = gt;
+        }
+        const Run sgt = shfl_run(lanes_inclusive(q), tp.gi);
+        const uint64_t sgidx = P.seg_super0[tp.seg] - P.seg_super0[P.seg_lo] + tp.sg;
+        Run prev = run_identity();
+        if (tp.sg > 0) {
+            bool ok = false;
+            wait.rearm();
+            for (;;) {
+                if (!ok) ok = run_get<false>(st.sgp_ll + 8 * (sgidx - 1), flag, prev);
+                if (wait.done(ok)) break;
+            }
+            prev.cnt = double(tp.sg) * double(kScanSuper) * double(kScanGroup) * double(kScanTile);
+        }
+        const Run sgp = run_combine(prev, sgt);
+        if (lane == 0) run_put<false>(st.sgp_ll + 8 * sgidx, sgp, flag);
+        if (!tp.last_in_seg) return;
+
+        // -- segment duty: the segment total goes to every rank's comm block (NVLink stores)
+        if (lane < P.world && !(P.flags & kScanSkipPublish))
+            run_put<true>(&st.peers[lane]->scan_ll[par][tp.seg][0], sgp, flag);
+    };
+
+    // ---- B of one tile: prefix from descriptors, scan, store ----------------------------------
+    auto do_b = [&](uint64_t tile) {
         const uint32_t m = scan_tile_count(P, tile);
-        // exclusive prefix of the tile: segment base (+) in-segment prefix
+        const TilePos tp = tile_pos(P, tile);
+        const uint64_t gidx = P.seg_group0[tp.seg] - P.seg_group0[P.seg_lo] + tp.g;
+        const uint64_t sgidx = P.seg_super0[tp.seg] - P.seg_super0[P.seg_lo] + tp.sg;
+        Run base = run_identity();
+        if (tp.j == 0) {
+            // first tile of a segment: segbase(s) = in-order fold of the totals of segments 0..s-1,
+            // which every rank stored into this comm block; published for the segment's other tiles
+            Run mine = run_identity();
+            bool ok = lane >= tp.seg;
+            wait.rearm();
+            for (;;) {
+                if (!ok) ok = run_get<true>(&st.comm->scan_ll[par][lane & (kSegments - 1)][0], flag, mine);
+                if (wait.done(ok)) break;
+            }
+            const int ls = lane & (kSegments - 1);
+            mine.cnt = scan_samples_in_tiles(P, P.seg_tile[ls], P.seg_tile[ls + 1]);
+            for (int s = 0; s < tp.seg; ++s) base = run_combine(base, shfl_run(mine, s));
+            if (lane == 0) run_put<false>(st.segbase_ll + 8 * tp.seg, base, flag);
+        }
+        // exclusive prefix of the tile: segbase (+) [(SGP(sg-1) (+) GTscan[gi-1]) (+) Ascan[k-1]]
         Run2 tile_excl;
         {
-            const int seg = scan_segment_of(P, tile);
-            const double* bp = st.segbase + 4 * seg;
-            const double* pp = st.prefix + 4 * (tile - P.tile_lo);
-            const Run base{dd{__ldcg(bp), __ldcg(bp + 1)}, dd{__ldcg(bp + 2), __ldcg(bp + 3)}, 0.0};
-            const Run pre{dd{__ldcg(pp), __ldcg(pp + 1)}, dd{__ldcg(pp + 2), __ldcg(pp + 3)},
-                          double((tile - P.seg_tile[seg]) * uint64_t(kScanTile))};
+            double s = 0.0, w = 0.0;
+            Run gt = run_identity(), prev = run_identity();
+            bool ok_a = lane >= tp.k, ok_g = lane >= tp.gi, ok_s = tp.sg == 0, ok_b = tp.j == 0;
+            const uint64_t* asrc = st.a_ll + 4 * (tile - P.tile_lo - tp.k + lane);
+            const uint64_t* gsrc = st.gt_ll + 8 * (gidx - tp.gi + lane);
+            wait.rearm();
+            for (;;) {
+                if (!ok_a) ok_a = ptx::ll_get<false>(asrc, flag, s) && ptx::ll_get<false>(asrc + 2, flag, w);
+                if (!ok_g) ok_g = run_get<false>(gsrc, flag, gt);
+                if (!ok_s) ok_s = run_get<false>(st.sgp_ll + 8 * (sgidx - 1), flag, prev);
+                if (!ok_b) ok_b = run_get<false>(st.segbase_ll + 8 * tp.seg, flag, base);
+                if (wait.done(ok_a && ok_g && ok_s && ok_b)) break;
+            }
+            Run a = run_identity();
+            if (lane < tp.k) a = run_from_tile(s, w, double(kScanTile));
+            const Run ainc = lanes_inclusive(a);
+            Run aexcl = shfl_run(ainc, tp.k > 0 ? tp.k - 1 : 0);
+            if (tp.k == 0) aexcl = run_identity();
+            Run gq = run_identity();
+            if (lane < tp.gi) gq = gt, gq.cnt = double(kScanGroup) * double(kScanTile);
+            const Run ginc = lanes_inclusive(gq);
+            Run gexcl = shfl_run(ginc, tp.gi > 0 ? tp.gi - 1 : 0);
+            if (tp.gi == 0) gexcl = run_identity();
+            prev.cnt = double(tp.sg) * double(kScanSuper) * double(kScanGroup) * double(kScanTile);
+            const Run pre = run_combine(run_combine(prev, gexcl), aexcl);
             tile_excl = scan_tile_exclusive(base, pre);
         }
         Run2 wpre{0.0, 0.0};   // fold of the passes before this one ("warps before mine")
@@ -428,55 +443,83 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
                     // The three scalars the callers print (4main.c:241 uses P[n-2]).
                     if (g + 1 == P.n || g + 2 == P.n) {
                         for (int r = 0; r < P.world; ++r) {
-                            double* fin = st.peers[r]->scan_final;
+                            uint64_t* fin = &st.peers[r]->scan_final_ll[par][0];
                             if (g + 1 == P.n) {
-                                ptx::st_relaxed_sys_f64(fin + 0, Pi);
-                                ptx::st_relaxed_sys_f64(fin + 1, Qi);
-                                if (P.n == 1) ptx::st_relaxed_sys_f64(fin + 2, 0.0);
+                                ptx::ll_put<true>(fin + 0, Pi, flag);
+                                ptx::ll_put<true>(fin + 2, Qi, flag);
+                                if (P.n == 1) ptx::ll_put<true>(fin + 4, 0.0, flag);
                             } else {
-                                ptx::st_relaxed_sys_f64(fin + 2, Pi);
+                                ptx::ll_put<true>(fin + 4, Pi, flag);
                             }
                         }
                     }
                 }
             }
         }
+    };
+
+    // ---- the tile loop -----------------------------------------------------------------------
+    // One GPU: a single pass, A + duties + B tile by tile.  Several GPUs: a rank's first store needs
+    // the lower ranks' segment totals, so all aggregates and duties come first, then all B parts.
+    const int sweeps = multi ? 2 : 1;
+#pragma unroll 1
+    for (int sweep = 0; sweep < sweeps; ++sweep) {
+#pragma unroll 1
+        for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
+            if (!multi || sweep == 0) do_a(tile);
+            if (!multi || sweep == 1) do_b(tile);
+        }
     }
 
-    // ---- end: second barrier, result -------------------------------------------
+    // ---- end: the last CTA collects the final scalars and writes the result ------------------
     __syncthreads();
     if (tid == 0) {
         if (multi) ptx::fence_sys(); else __threadfence();
-        sm.is_last = (atomicAdd(st.ticket_b, 1u) == gridDim.x - 1);
+        sm.is_last = (atomicAdd(st.ticket, 1u) == gridDim.x - 1);
     }
     __syncthreads();
     if (!sm.is_last || warp != 0) return;
-    int status = sm.status;
-    if (multi) {
-        ptx::fence_sys();
-        const uint64_t epoch = st.comm->scan_epoch;
+    if (multi) ptx::fence_sys(); else __threadfence();
+    if (replicate) {
+        // Fused all-gather: every rank tells every rank "my stores into your tables are complete"
+        // (a release store after the system fence above) and waits for the same word from everyone;
+        // when the kernel retires, this GPU's tables are whole.
         if (lane < P.world && !(P.flags & kScanSkipPublish))
-            ptx::red_release_sys_add(&st.peers[lane]->scan_done, 1ull);
-        __syncwarp();
-        if (lane == 0) {
-            if (!spin_until(&st.comm->scan_done, uint64_t(P.world) * (epoch + 1), true, limit))
-                status = BQ_ERR_TIMEOUT;
-            st.comm->scan_epoch = epoch + 1;
+            ptx::st_release_sys_u64(&st.peers[lane]->scan_done_ll[par][P.rank], uint64_t(flag));
+        bool ok = lane >= P.world;
+        wait.rearm();
+        for (;;) {
+            if (!ok) ok = ptx::ld_acquire_sys(&st.comm->scan_done_ll[par][lane & (BQ_MAX_WORLD - 1)]) == uint64_t(flag);
+            if (wait.done(ok)) break;
         }
     }
+    // P[n-1], Q[n-1], P[n-2]: stored by whichever rank holds the end of the grid into every comm block
+    double fin = 0.0;
+    {
+        bool ok = lane >= 3;
+        wait.rearm();
+        for (;;) {
+            if (!ok) ok = ptx::ll_get<true>(&st.comm->scan_final_ll[par][2 * (lane & 3)], flag, fin);
+            if (wait.done(ok)) break;
+        }
+    }
+    const double p_last = __shfl_sync(0xffffffffu, fin, 0), q_last = __shfl_sync(0xffffffffu, fin, 1),
+                 p_second = __shfl_sync(0xffffffffu, fin, 2);
     if (lane == 0) {
+        const bool aborted = ptx::ld_acquire_gpu(st.abort_word) == gen;
         bq_scan_result* R = st.result;
-        R->p_last = ptx::ld_relaxed_sys_f64(st.comm->scan_final + 0);
-        R->q_last = ptx::ld_relaxed_sys_f64(st.comm->scan_final + 1);
-        R->p_second_last = ptx::ld_relaxed_sys_f64(st.comm->scan_final + 2);
+        R->p_last = p_last;
+        R->q_last = q_last;
+        R->p_second_last = p_second;
         R->slice_begin = P.tile_lo * uint64_t(kScanTile);
         uint64_t e = P.tile_hi * uint64_t(kScanTile);
         R->slice_end = e < P.n ? e : P.n;
-        if (status != BQ_OK) R->status = status;
+        R->status = (aborted || wait.failed) ? BQ_ERR_TIMEOUT : BQ_OK;
         R->world = P.world;
         R->rank = P.rank;
-        *st.ticket_b = 0u;
-        st.ready[1] = gen;             // generation completed
+        R->reserved[0] = R->reserved[1] = 0;
+        *st.ticket = 0u;
+        st.comm->scan_epoch = gen;     // generation completed: the next launch uses gen + 1
         R->t_end_ns = ptx::globaltimer();
     }
     // device -> host leg: the result block goes straight into pinned mapped host memory

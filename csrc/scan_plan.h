@@ -7,9 +7,21 @@
 //   segment = one of 8 near-equal runs of tiles (fixed by n alone)
 //   rank r of a world of 1/2/4/8 owns 8/world consecutive segments
 //
-// Tile prefixes are built per segment with a fixed-shape block scan and the
-// segment bases by an in-order fold over the 8 segment totals, so the tables
-// are bit-identical for every world size.
+// Inside a segment the tiles form groups of 32 and the groups supergroups of 32.
+// The exclusive prefix of a tile is a fixed-shape expression of tile aggregates:
+//
+//   prefix(tile) = segbase(s) (+) [ (SGP(sg-1) (+) GTscan(sg)[gi-1]) (+) Ascan(g)[k-1] ]
+//
+//   Ascan(g)   Kogge-Stone inclusive scan over the (up to) 32 tile aggregates of group g
+//   GT(g)      group total = last valid element of Ascan(g)
+//   GTscan(sg) the same scan over the group totals of supergroup sg
+//   SGP(sg)    in-order fold of the supergroup totals 0..sg of the segment
+//   segbase(s) in-order fold of the totals of segments 0..s-1 (all ranks)
+//
+// Every element depends on earlier tiles only and on nothing but n, so (a) the
+// tables are bit-identical for every world size, grid and schedule, and (b) a
+// tile can form its prefix by itself as soon as its few inputs exist — which
+// is what lets one GPU run the scan in a single pass (scan_kernel.cu).
 #pragma once
 #include <stdint.h>
 
@@ -22,6 +34,8 @@ constexpr int kScanThreads = 256;
 constexpr int kScanItems = 8;
 constexpr int kScanTile = kScanThreads * kScanItems;   // 2048 samples
 constexpr uint64_t kScanMaxN = 1ull << 34;
+constexpr int kScanGroup = 32;                          // tiles per group (one warp lane each)
+constexpr int kScanSuper = 32;                          // groups per supergroup
 
 enum ScanFlags : uint32_t {
     kScanReplicate = 1u,
@@ -40,6 +54,8 @@ struct ScanPlan {
     uint32_t timeout_ms;
     uint64_t n_tiles;
     uint64_t seg_tile[kSegments + 1];   // segment s = tiles [seg_tile[s], seg_tile[s+1])
+    uint64_t seg_group0[kSegments + 1];   // groups of all segments before s (index of s's first group)
+    uint64_t seg_super0[kSegments + 1];   // same for supergroups
     uint32_t seg_lo, seg_hi;            // segments owned by this rank
     uint64_t tile_lo, tile_hi;          // == seg_tile[seg_lo], seg_tile[seg_hi]
 };

@@ -237,6 +237,10 @@ int bq_cumulative(bq_ctx* ctx, const bq_scan_job* job, double* dP, double* dQ, d
 int bq_cumulative_async(bq_ctx* ctx, const bq_scan_job* job, double* dP, double* dQ,
                         double* dSamples, void* stream);
 int bq_scan_result_fetch(bq_ctx* ctx, bq_scan_result* out);
+/* The scan's descriptor scratch grows with n on first use (cudaMalloc, which synchronises and
+ * cannot be captured): size it for grids of up to n samples ahead of a latency-critical call or
+ * a stream capture. */
+int bq_ctx_reserve_scan(bq_ctx* ctx, uint64_t n);
 
 /* Cumulative integration that allocates nothing (no counterpart in the
  * reference, which cudaMallocs and frees on every run: cintegrate.cu:116-118,
