@@ -109,6 +109,13 @@ def _declare(lib, cuda):
     sig("bq_ctx_export_comm", i32, vp, C.c_char_p)
     sig("bq_ctx_attach_peers", i32, vp, i32, i32, C.c_char_p)
     sig("bq_ctx_reset_comm", i32, vp)
+    sig("bq_ctx_adopt_comm", i32, vp, i32, i32, P(vp), vp, C.c_size_t)
+    sig("bq_ctx_set_nvls", i32, vp, i32)
+    sig("bq_ctx_set_scan_multicast", i32, vp, vp, vp)
+    sig("bq_world_has_multicast", i32, vp)
+    sig("bq_world_set_nvls", i32, vp, i32)
+    sig("bq_world_alloc_tables", i32, vp, u64, P(vp), P(vp))
+    sig("bq_world_free_tables", None, vp)
     sig("bq_ipc_export", i32, vp, C.c_char_p)
     sig("bq_ipc_export_at", i32, vp, C.c_char_p, P(u64))
     sig("bq_ipc_open", i32, C.c_char_p, P(vp))

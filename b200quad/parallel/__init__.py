@@ -181,10 +181,40 @@ class LocalWorld:
               "bq_world_cumulative")
         return list(out)
 
+    # -- NVLS (NVSwitch multicast) ---------------------------------------------------
+    @property
+    def has_multicast(self):
+        return bool(self.lib.bq_world_has_multicast(self.handle))
+
+    def set_nvls(self, on=True):
+        """Publish through the multicast address (one multimem.st per word / per 16 bytes of a
+        replicated table) instead of one store per peer.  Same results either way."""
+        check(self.lib.bq_world_set_nvls(self.handle, 1 if on else 0), "bq_world_set_nvls")
+
+    def alloc_tables(self, n):
+        """P and Q tables of n doubles on every rank, in symmetric multicast-bound memory; returns
+        two lists of device addresses (rank order).  Freed by free_tables() or with the world."""
+        aP = (C.c_void_p * self.size)()
+        aQ = (C.c_void_p * self.size)()
+        check(self.lib.bq_world_alloc_tables(self.handle, int(n), aP, aQ), "bq_world_alloc_tables")
+        return [int(p) for p in aP], [int(q) for q in aQ]
+
+    def free_tables(self):
+        self.lib.bq_world_free_tables(self.handle)
+
     def close(self):
         if self.handle:
             self.lib.bq_world_destroy(self.handle)
             self.handle = None
+
+
+def device_tensor(ptr, n, device):
+    """A float64 torch tensor over `n` doubles at device address `ptr` (memory owned by the library)."""
+    import torch
+
+    class _Raw:
+        __cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f8", "data": (int(ptr), False), "version": 3}
+    return torch.as_tensor(_Raw(), device=torch.device("cuda", device))
 
 
 def local_world(size):
@@ -214,15 +244,84 @@ class DistWorld:
         # context that single-GPU calls use (parallel.context()) must stay untouched.
         self.ctx = Context(device)
         lib = self.ctx.lib
-        mine = C.create_string_buffer(_native.IPC_HANDLE_BYTES)
-        check(lib.bq_ctx_export_comm(self.ctx.handle, mine), "bq_ctx_export_comm")
-        gathered = [None] * self.size
-        dist.all_gather_object(gathered, bytes(mine.raw), group=group)
-        blob = b"".join(gathered)
-        check(lib.bq_ctx_attach_peers(self.ctx.handle, self.rank, self.size, blob),
-              "bq_ctx_attach_peers")
+        self.transport = None
+        self._symm = []                       # keeps the symmetric tensors (and their handles) alive
+        if os.environ.get("BQ_SYMM", "0") == "1":     # opt-in: CUDA IPC is the default wiring
+            self._wire_symmetric(device)
+        if self.transport is None:
+            mine = C.create_string_buffer(_native.IPC_HANDLE_BYTES)
+            check(lib.bq_ctx_export_comm(self.ctx.handle, mine), "bq_ctx_export_comm")
+            gathered = [None] * self.size
+            dist.all_gather_object(gathered, bytes(mine.raw), group=group)
+            blob = b"".join(gathered)
+            check(lib.bq_ctx_attach_peers(self.ctx.handle, self.rank, self.size, blob),
+                  "bq_ctx_attach_peers")
+            self.transport = "cuda-ipc"
         self.ctx.rank, self.ctx.world = self.rank, self.size
         dist.barrier(group=group)
+
+    def _symm_alloc(self, nbytes, device):
+        """(tensor, handle) of a torch symmetric-memory allocation, rendezvoused over the group."""
+        import torch
+        import torch.distributed._symmetric_memory as symm_mem
+        t = symm_mem.empty(int(nbytes), dtype=torch.uint8, device=torch.device("cuda", device))
+        group = self.group if self.group is not None else self.dist.group.WORLD
+        hdl = symm_mem.rendezvous(t, group)
+        return t, hdl
+
+    def _wire_symmetric(self, device):
+        """Comm blocks in torch symmetric memory (cuMem allocations exchanged by the process group,
+        bound to an NVLS multicast object when the fabric has one): peers are plain mapped pointers
+        and, with multicast, one multimem.st reaches every rank.  Falls back to CUDA IPC when the
+        build or the box cannot do it; every rank takes the same branch (the decision is agreed)."""
+        import torch
+        ok, t, hdl = 1, None, None
+        try:
+            t, hdl = self._symm_alloc(4096, device)
+            t.zero_()
+            torch.cuda.synchronize(device)
+            ptrs = [int(p) for p in hdl.buffer_ptrs]
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            if len(ptrs) != self.size or any(p == 0 for p in ptrs):
+                ok = 0
+        except Exception:
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=torch.device("cuda", device))
+        self.dist.all_reduce(flag, op=self.dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) != 1:
+            return
+        arr = (C.c_void_p * _native.MAX_WORLD)(*ptrs)
+        check(self.ctx.lib.bq_ctx_adopt_comm(self.ctx.handle, self.rank, self.size, arr, C.c_void_p(mc or None), 4096),
+              "bq_ctx_adopt_comm")
+        self._symm.append((t, hdl))
+        self.has_multicast = mc != 0
+        self.transport = "symmetric-memory" + ("+multicast" if mc else "")
+
+    has_multicast = False
+
+    def set_nvls(self, on=True):
+        check(self.ctx.lib.bq_ctx_set_nvls(self.ctx.handle, 1 if on else 0), "bq_ctx_set_nvls")
+
+    def symmetric_tables(self, n):
+        """Full-size P and Q tables in symmetric memory: returns (P, Q) float64 tensors; every
+        rank's copies are wired as scan peers (and as multicast targets when available)."""
+        import torch
+        device = self.ctx.device
+        out = []
+        peers, mcs = [], []
+        for _ in range(2):
+            t, hdl = self._symm_alloc(int(n) * 8, device)
+            self._symm.append((t, hdl))
+            out.append(t.view(torch.float64))
+            peers.append([int(p) for p in hdl.buffer_ptrs])
+            mcs.append(int(getattr(hdl, "multicast_ptr", 0) or 0))
+        aP = (C.c_void_p * _native.MAX_WORLD)(*peers[0])
+        aQ = (C.c_void_p * _native.MAX_WORLD)(*peers[1])
+        check(self.ctx.lib.bq_ctx_set_scan_peers(self.ctx.handle, aP, aQ), "bq_ctx_set_scan_peers")
+        check(self.ctx.lib.bq_ctx_set_scan_multicast(self.ctx.handle, C.c_void_p(mcs[0] or None),
+                                                     C.c_void_p(mcs[1] or None)), "bq_ctx_set_scan_multicast")
+        self.dist.barrier(group=self.group)
+        return out[0], out[1]
 
     def integrate(self, job):
         return self.ctx.integrate(job)

@@ -30,7 +30,7 @@ NVCC_FLAGS = os.environ.get("BQ_NVCC_EXTRA", "").split() + ["-std=c++17", "-O3",
 CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-Wall", "-Wno-unknown-pragmas",
              "-Wno-unused-function"]
 
-CUDA_SOURCES = ["quad_kernel.cu", "scan_kernel.cu", "ctx.cu", "scan_host.cu", "noalloc.cu", "drv.cu"]
+CUDA_SOURCES = ["quad_kernel.cu", "scan_kernel.cu", "ctx.cu", "scan_host.cu", "noalloc.cu", "drv.cu", "symm.cu"]
 HOST_SOURCES = ["host_common.cpp", "cpu_backend.cpp", "cpu_scan.cpp"]
 CPU_ONLY_SOURCES = ["cuda_stubs.cpp"]     # the CUDA entry points as stubs: only in libb200quad_cpu.so
 SAN_FLAGS = ["-fsanitize=address,undefined", "-fno-omit-frame-pointer", "-fno-sanitize-recover=undefined", "-g"]

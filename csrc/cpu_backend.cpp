@@ -114,7 +114,7 @@ struct CpuWorker {
                 TileAcc<R>& acc = accs[t];
                 double rb = row_base_index(P, g, 0);
                 constexpr bool fused = F::kFusedSum;
-                const bool fast = F::kTrig && (P.flags & kFlagFastTrig);
+                const int fast = !(F::kTrig && (P.flags & kFlagFastTrig)) ? 0 : ((P.flags & kFlagRowK) ? 2 : 1);
                 double dcol[kCols];
                 for (int j = 0; j < kCols; ++j) dcol[j] = dxt[j];
                 for (uint32_t r = 0; r < g.full_rows; ++r) {
@@ -126,10 +126,12 @@ struct CpuWorker {
                         if (rotate) {
                             for (int j = 0; j < kCols; ++j)
                                 v[j] = point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j], X0[r], dxt[j]);
-                        } else if (fast) {
-                            RowDirect<F, R, true>::eval(f, rb, dcol, P.h, P.a, v);
+                        } else if (fast == 2) {
+                            RowDirect<F, R, 2>::eval(f, rb, dcol, P.h, P.a, v);
+                        } else if (fast == 1) {
+                            RowDirect<F, R, 1>::eval(f, rb, dcol, P.h, P.a, v);
                         } else {
-                            RowDirect<F, R, false>::eval(f, rb, dcol, P.h, P.a, v);
+                            RowDirect<F, R, 0>::eval(f, rb, dcol, P.h, P.a, v);
                         }
                         acc.add_row(v);
                     }
@@ -144,8 +146,8 @@ struct CpuWorker {
                             else
                                 acc.add_one(j, rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j],
                                                                            X0[r], dxt[j])
-                                                      : fast ? point_direct<F, R, true>(f, rb, dxt[j], P.h, P.a)
-                                                             : point_direct<F, R, false>(f, rb, dxt[j], P.h, P.a));
+                                                      : fast ? point_direct<F, R, 1>(f, rb, dxt[j], P.h, P.a)
+                                                             : point_direct<F, R, 0>(f, rb, dxt[j], P.h, P.a));
                         }
                 }
                 if (((tile - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || tile + 1 == hi) {

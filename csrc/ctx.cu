@@ -19,6 +19,7 @@
 #include "nvtx_range.h"
 #include "quad_launch.h"
 #include "scan_launch.h"
+#include "symm.h"
 
 namespace bq {
 
@@ -47,6 +48,7 @@ struct DeviceGuard {
 
 namespace bq {
 static int ctx_init(bq_ctx* c, int device);
+static int ctx_adopt_comm(bq_ctx* c, CommBlock* own, CommBlock* mc);
 }
 using namespace bq;
 
@@ -142,7 +144,7 @@ void bq_ctx_destroy(bq_ctx* c) {
     cudaFree(c->d_ticket);
     cudaFree(c->d_result);
     cudaFree(c->d_scan_result);
-    cudaFree(c->d_comm);
+    if (!c->comm_external) cudaFree(c->d_comm);
     cudaFree(c->d_table);
     cudaFree(c->d_trace);
     cudaFreeHost(c->h_result);
@@ -229,6 +231,17 @@ int bq_ctx_inject_fault(bq_ctx* c, int kind) {
 
 namespace bq {
 
+// The comm block of a context moves into memory someone else owns (symmetric / multicast-bound).
+static int ctx_adopt_comm(bq_ctx* c, CommBlock* own, CommBlock* mc) {
+    DeviceGuard guard(c->device);
+    BQ_CUDA(cudaStreamSynchronize(c->stream));
+    if (!c->comm_external && c->d_comm) BQ_CUDA(cudaFree(c->d_comm));
+    c->d_comm = own;
+    c->comm_external = true;
+    c->mc_comm = mc;
+    return BQ_OK;
+}
+
 int order_after_previous(bq_ctx* c, cudaStream_t stream) {
     if (!c->last_stream || c->last_stream == stream) return BQ_OK;
     cudaStreamCaptureStatus a = cudaStreamCaptureStatusNone, b = cudaStreamCaptureStatusNone;
@@ -286,6 +299,7 @@ static int quad_enqueue(bq_ctx* c, const bq_job* job, int rank, int world, uint3
     st.comm = c->d_comm;
     for (int r = 0; r < BQ_MAX_WORLD; ++r) st.peers[r] = c->peers[r];
     st.peers[rank] = c->d_comm;
+    st.mc_comm = (c->use_nvls && world == c->world) ? c->mc_comm : nullptr;
     st.table = c->d_table;
     st.seg_out = seg_out;
     st.trace = c->d_trace;
@@ -469,6 +483,53 @@ int bq_ctx_attach_peers(bq_ctx* c, int rank, int world, const unsigned char* han
     return BQ_OK;
 }
 
+int bq_ctx_adopt_comm(bq_ctx* c, int rank, int world, void* const* comm_ptrs, void* mc_ptr, size_t bytes) {
+    if (!c || !comm_ptrs || rank < 0 || rank >= world || world > BQ_MAX_WORLD || (kSegments % world) != 0 ||
+        bytes < sizeof(CommBlock)) {
+        set_error("adopt_comm: bad rank/world %d/%d or block smaller than %zu bytes", rank, world, sizeof(CommBlock));
+        return BQ_ERR_INVALID;
+    }
+    for (int r = 0; r < world; ++r)
+        if (!comm_ptrs[r] || (uintptr_t(comm_ptrs[r]) & 255)) {
+            set_error("adopt_comm: comm block of rank %d is null or not 256-byte aligned", r);
+            return BQ_ERR_INVALID;
+        }
+    DeviceGuard guard(c->device);
+    BQ_CUDA(cudaStreamSynchronize(c->last_stream ? c->last_stream : c->stream));
+    for (int r = 0; r < BQ_MAX_WORLD; ++r) {
+        if (c->peer_ipc[r] && c->peers[r]) cudaIpcCloseMemHandle(c->peers[r]);
+        c->peers[r] = nullptr;
+        c->peer_ipc[r] = false;
+    }
+    const int rc = ctx_adopt_comm(c, static_cast<CommBlock*>(comm_ptrs[rank]), static_cast<CommBlock*>(mc_ptr));
+    if (rc != BQ_OK) return rc;
+    BQ_CUDA(cudaMemset(c->d_comm, 0, sizeof(CommBlock)));
+    BQ_CUDA(cudaDeviceSynchronize());
+    for (int r = 0; r < world; ++r) c->peers[r] = static_cast<CommBlock*>(comm_ptrs[r]);
+    c->rank = rank;
+    c->world = world;
+    const char* env = getenv("BQ_NVLS");
+    c->use_nvls = mc_ptr != nullptr && env && env[0] == '1';
+    return BQ_OK;
+}
+
+int bq_ctx_set_nvls(bq_ctx* c, int on) {
+    if (!c) return BQ_ERR_INVALID;
+    if (on && !c->mc_comm) {
+        set_error("NVLS multicast is not available for this context");
+        return BQ_ERR_UNSUPPORTED;
+    }
+    c->use_nvls = on != 0;
+    return BQ_OK;
+}
+
+int bq_ctx_set_scan_multicast(bq_ctx* c, double* mcP, double* mcQ) {
+    if (!c) return BQ_ERR_INVALID;
+    c->scan_mcP = mcP;
+    c->scan_mcQ = mcQ;
+    return BQ_OK;
+}
+
 int bq_ctx_reset_comm(bq_ctx* c) {
     if (!c) return BQ_ERR_INVALID;
     DeviceGuard guard(c->device);
@@ -485,6 +546,8 @@ int bq_ctx_reset_comm(bq_ctx* c) {
 
 struct bq_world {
     std::vector<bq_ctx*> ctx;
+    bq::SymmAlloc comm;                   // the comm blocks as one symmetric, multicast-bound allocation
+    std::vector<bq::SymmAlloc> tables;    // bq_world_alloc_tables
 };
 
 int bq_world_create(int ndev, const int* devices, bq_world** out) {
@@ -501,6 +564,24 @@ int bq_world_create(int ndev, const int* devices, bq_world** out) {
             return rc;
         }
         w->ctx.push_back(c);
+    }
+    // Comm blocks: one symmetric allocation (a copy per GPU, every copy mapped for every GPU) bound
+    // to an NVLS multicast object when the fabric offers one; else each context keeps its own
+    // cudaMalloc'd block and peers reach it through peer access.
+    if (ndev > 1) {
+        int devs[BQ_MAX_WORLD];
+        for (int r = 0; r < ndev; ++r) devs[r] = w->ctx[r]->device;
+        if (symm_create(devs, ndev, sizeof(CommBlock), /*want_mc=*/true, &w->comm) == BQ_OK) {
+            const char* env = getenv("BQ_NVLS");
+            const bool nvls = w->comm.mc != nullptr && env && env[0] == '1';
+            for (int r = 0; r < ndev; ++r) {
+                if (ctx_adopt_comm(w->ctx[r], (CommBlock*)w->comm.uc[r], (CommBlock*)w->comm.mc) != BQ_OK) {
+                    bq_world_destroy(w);
+                    return BQ_ERR_CUDA;
+                }
+                w->ctx[r]->use_nvls = nvls;
+            }
+        }
     }
     for (int r = 0; r < ndev; ++r) {
         bq_ctx* c = w->ctx[r];
@@ -533,8 +614,56 @@ int bq_world_create(int ndev, const int* devices, bq_world** out) {
 
 void bq_world_destroy(bq_world* w) {
     if (!w) return;
-    for (bq_ctx* c : w->ctx) bq_ctx_destroy(c);
+    for (bq_ctx* c : w->ctx) bq_ctx_destroy(c);     // synchronises every stream first
+    for (SymmAlloc& t : w->tables) symm_destroy(&t);
+    symm_destroy(&w->comm);
     delete w;
+}
+
+int bq_world_has_multicast(const bq_world* w) { return (w && w->comm.mc) ? 1 : 0; }
+
+int bq_world_set_nvls(bq_world* w, int on) {
+    if (!w) return BQ_ERR_INVALID;
+    if (on && !w->comm.mc) {
+        set_error("NVLS multicast is not available for this world (driver / fabric)");
+        return BQ_ERR_UNSUPPORTED;
+    }
+    for (bq_ctx* c : w->ctx) c->use_nvls = on != 0;
+    return BQ_OK;
+}
+
+int bq_world_alloc_tables(bq_world* w, uint64_t n, double** P, double** Q) {
+    if (!w || !P || !Q || n < 1) return BQ_ERR_INVALID;
+    const int nd = int(w->ctx.size());
+    int devs[BQ_MAX_WORLD];
+    for (int r = 0; r < nd; ++r) devs[r] = w->ctx[r]->device;
+    for (int k = 0; k < 2; ++k) {
+        SymmAlloc a;
+        const int rc = symm_create(devs, nd, size_t(n) * sizeof(double), /*want_mc=*/true, &a);
+        if (rc != BQ_OK) return rc;
+        w->tables.push_back(a);
+        for (int r = 0; r < nd; ++r) (k == 0 ? P : Q)[r] = static_cast<double*>(a.uc[r]);
+    }
+    return BQ_OK;
+}
+
+void bq_world_free_tables(bq_world* w) {
+    if (!w) return;
+    for (bq_ctx* c : w->ctx) {
+        DeviceGuard guard(c->device);
+        cudaStreamSynchronize(c->last_stream ? c->last_stream : c->stream);
+        c->scan_mcP = c->scan_mcQ = nullptr;
+    }
+    for (SymmAlloc& t : w->tables) symm_destroy(&t);
+    w->tables.clear();
+}
+
+// Multicast address of a table handed out by bq_world_alloc_tables (null for any other pointer).
+double* bq_world_table_multicast(bq_world* w, const double* rank0_ptr) {
+    if (!w) return nullptr;
+    for (SymmAlloc& t : w->tables)
+        if (t.uc[0] == rank0_ptr) return static_cast<double*>(t.mc);
+    return nullptr;
 }
 
 int bq_world_size(const bq_world* w) { return w ? int(w->ctx.size()) : 0; }

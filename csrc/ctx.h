@@ -33,6 +33,9 @@ struct bq_ctx {
     bq_result* d_result = nullptr;
     bq_scan_result* d_scan_result = nullptr;
     bq::CommBlock* d_comm = nullptr;
+    bool comm_external = false;           // d_comm lives in symmetric memory owned by the world / the caller
+    bq::CommBlock* mc_comm = nullptr;     // NVLS multicast address of every rank's comm block (or null)
+    bool use_nvls = false;                // publish through mc_comm (multimem.st) instead of per-peer stores
     double* d_table = nullptr;
     uint64_t* d_trace = nullptr;          // per-CTA timeline, allocated by bq_ctx_trace(on)
     int trace_ctas = 0;
@@ -45,6 +48,8 @@ struct bq_ctx {
     uint64_t scan_tiles_cap = 0;
     double* scan_peerP[BQ_MAX_WORLD] = {};
     double* scan_peerQ[BQ_MAX_WORLD] = {};
+    double* scan_mcP = nullptr;           // multicast addresses of the replicated tables (or null)
+    double* scan_mcQ = nullptr;
     int scan_grid = 0;
 
     // pinned staging

@@ -43,6 +43,9 @@ int bq_cumulative_noalloc(int, const bq_scan_job*, double*, double*, bq_scan_res
 int bq_ctx_export_comm(bq_ctx*, unsigned char*) { return unsupported("bq_ctx_export_comm"); }
 int bq_ctx_attach_peers(bq_ctx*, int, int, const unsigned char*) { return unsupported("bq_ctx_attach_peers"); }
 int bq_ctx_reset_comm(bq_ctx*) { return unsupported("bq_ctx_reset_comm"); }
+int bq_ctx_adopt_comm(bq_ctx*, int, int, void* const*, void*, size_t) { return unsupported("bq_ctx_adopt_comm"); }
+int bq_ctx_set_nvls(bq_ctx*, int) { return unsupported("bq_ctx_set_nvls"); }
+int bq_ctx_set_scan_multicast(bq_ctx*, double*, double*) { return unsupported("bq_ctx_set_scan_multicast"); }
 int bq_ipc_export(void*, unsigned char*) { return unsupported("bq_ipc_export"); }
 int bq_ipc_export_at(void*, unsigned char*, uint64_t*) { return unsupported("bq_ipc_export_at"); }
 int bq_ipc_open(const unsigned char*, void**) { return unsupported("bq_ipc_open"); }
@@ -55,6 +58,11 @@ int bq_world_create(int, const int*, bq_world** out) {
 void bq_world_destroy(bq_world*) {}
 int bq_world_size(const bq_world*) { return 0; }
 bq_ctx* bq_world_ctx(bq_world*, int) { return nullptr; }
+int bq_world_has_multicast(const bq_world*) { return 0; }
+int bq_world_set_nvls(bq_world*, int) { return unsupported("bq_world_set_nvls"); }
+int bq_world_alloc_tables(bq_world*, uint64_t, double**, double**) { return unsupported("bq_world_alloc_tables"); }
+void bq_world_free_tables(bq_world*) {}
+double* bq_world_table_multicast(bq_world*, const double*) { return nullptr; }
 int bq_world_integrate(bq_world*, const bq_job*, bq_result*) { return unsupported("bq_world_integrate"); }
 int bq_world_cumulative(bq_world*, const bq_scan_job*, double* const*, double* const*, bq_scan_result*) { return unsupported("bq_world_cumulative"); }
 int bq_integrate_local_async(bq_ctx*, const bq_job*, int, int, double*, void*) { return unsupported("bq_integrate_local_async"); }

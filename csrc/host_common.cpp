@@ -160,7 +160,10 @@ int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, in
     if (trig) {
         const double w = fabs(P->omega);
         const double amax = (fabs(job.a) > fabs(job.b) ? fabs(job.a) : fabs(job.b)) + fabs(P->h);
-        if (w * amax <= kFastTrigMax) P->flags |= kFlagFastTrig;
+        if (w * amax <= kFastTrigMax) {
+            P->flags |= kFlagFastTrig;
+            if (w * fabs(P->h) * double(kWidth) <= 1.0 / 1024.0) P->flags |= kFlagRowK;
+        }
     }
     P->timeout_ms = 2000;
     return BQ_OK;

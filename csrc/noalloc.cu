@@ -14,7 +14,7 @@
 // the generation word, the result block and a copy of the velocity table) lives
 // in ONE file-scope `static __device__ __align__(256)` array below.  Its size is
 // fixed at build time, which is what bounds n (BQ_NOALLOC_MAX_SAMPLES).  Every
-// GPU that loads this library carries the array (about 1.2 MB) until the process
+// GPU that loads this library carries the array (about 3.3 MB) until the process
 // exits.  It always integrates the library's default velocity table: a table set
 // with bq_ctx_set_profile belongs to a context, and this entry point has none.
 //
@@ -182,7 +182,9 @@ int bq_cumulative_noalloc(int device, const bq_scan_job* job, double* dP, double
     memset(&state, 0, sizeof(state));
     constexpr ScanScratchLayout L = scan_scratch_layout(kNoAllocMaxTiles);
     state.a_ll = reinterpret_cast<uint64_t*>(sc->desc + L.a_off);
+    state.aex_ll = reinterpret_cast<uint64_t*>(sc->desc + L.aex_off);
     state.gt_ll = reinterpret_cast<uint64_t*>(sc->desc + L.gt_off);
+    state.head_ll = reinterpret_cast<uint64_t*>(sc->desc + L.head_off);
     state.sgp_ll = reinterpret_cast<uint64_t*>(sc->desc + L.sgp_off);
     state.segbase_ll = sc->segbase_ll;
     state.abort_word = &sc->control.abort_word;

@@ -43,6 +43,7 @@ enum PlanFlags : uint32_t {
     kFlagLocalOnly = 1u,     // skip the cross-GPU stage, leave segment pairs in seg_out
     kFlagSkipPublish = 2u,   // fault injection: never publish (peers time out)
     kFlagFastTrig = 4u,      // DIRECT: |angle| <= kFastTrigMax over [a, b], bounded sin/cos allowed
+    kFlagRowK = 8u,          // ... and a row of a thread spans < 2^-10 rad: its samples share one multiple of pi/2
 };
 
 struct Plan {

@@ -98,6 +98,15 @@ __device__ __forceinline__ bool ll_get(const uint64_t* src, uint32_t flag, doubl
 __device__ __forceinline__ void multimem_st_u64(uint64_t* mc, uint64_t v) {
     asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
 }
+// 16 bytes (two doubles) to a multicast address: the switch writes them into every GPU's copy.
+// (multimem.st has no .f64 vector form; the two doubles travel as four 32-bit lanes, bit for bit.)
+__device__ __forceinline__ void multimem_st_f64x2(double* mc, double a, double b) {
+    const unsigned long long ua = (unsigned long long)__double_as_longlong(a), ub = (unsigned long long)__double_as_longlong(b);
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc),
+                 "f"(__uint_as_float(unsigned(ua))), "f"(__uint_as_float(unsigned(ua >> 32))),
+                 "f"(__uint_as_float(unsigned(ub))), "f"(__uint_as_float(unsigned(ub >> 32)))
+                 : "memory");
+}
 __device__ __forceinline__ void multimem_red_add_u64(uint64_t* mc, uint64_t v) {
     asm volatile("multimem.red.release.sys.global.add.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
 }

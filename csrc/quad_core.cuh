@@ -38,16 +38,18 @@ BQ_HD R point_rotate(const F& f, R S, R C, R cj, R sj, double x0, double dx) {
 
 // DIRECT: x = a + (i + off) * h with a single rounding (the index arithmetic
 // rowbase + col is exact in fp64 below 2^52), then a plain call of f.
-// FAST: the plan has verified the argument range of the bounded sin/cos (kFlagFastTrig).
-template <class F, class R, bool FAST = false>
+// FAST: 0 = libm / libdevice; 1 = the plan has verified the argument range of the bounded sin/cos
+// (kFlagFastTrig); 2 = as 1, and the samples of a row share one multiple of pi/2 (kFlagRowK; only
+// whole rows differ, a single point is evaluated as in 1).
+template <class F, class R, int FAST = 0>
 BQ_HD R point_direct(const F& f, double rowbase, double col, double h, double a) {
     double x = fma(rowbase + col, h, a);
-    if constexpr (FAST) return f.template eval_fast<R>(R(x));
+    if constexpr (FAST != 0) return f.template eval_fast<R>(R(x));
     return f.template eval<R>(R(x));
 }
 
 // DIRECT: the kCols samples of one row of one thread (columns kThreads points apart).
-template <class F, class R, bool FAST>
+template <class F, class R, int FAST>
 struct RowDirect {
     static BQ_HD void eval(const F& f, double rowbase, const double (&col)[kCols], double h, double a,
                            R (&v)[kCols]) {
@@ -60,7 +62,7 @@ struct RowDirect {
 // (nearly always: neighbouring samples are a tiny angle apart) runs the unselected sine or cosine
 // polynomial — the selected form costs 20 select instructions per sample, more issue slots than
 // its 12 fp64 operations; both forms produce the same bits (integrands.cuh).
-template <class F>
+template <class F, bool ROWK>
 struct RowDirectTrig {
     static BQ_HD void eval(const F& f, double rowbase, const double (&col)[kCols], double h, double a,
                            double (&v)[kCols]) {
@@ -70,14 +72,21 @@ struct RowDirectTrig {
 #pragma unroll
         for (int j = 0; j < kCols; ++j) {
             x[j] = fma(rowbase + col[j], h, a);
-            red[j] = trig_reduce<COS>(f.angle_fast(x[j]));
+            if (ROWK && j > 0)
+                red[j] = trig_reduce_with<COS>(f.angle_fast(x[j]), red[0]);
+            else
+                red[j] = trig_reduce<COS>(f.angle_fast(x[j]));
         }
         double val[kCols];
         bool done = false;
 #if defined(__CUDA_ARCH__)
         unsigned odd = 0;
+        if (ROWK) {
+            odd = (red[0].q & 1) ? (1u << kCols) - 1u : 0u;     // one quadrant for the whole row
+        } else {
 #pragma unroll
-        for (int j = 0; j < kCols; ++j) odd |= unsigned(red[j].q & 1) << j;
+            for (int j = 0; j < kCols; ++j) odd |= unsigned(red[j].q & 1) << j;
+        }
         if (__all_sync(0xffffffffu, odd == 0u)) {
 #pragma unroll
             for (int j = 0; j < kCols; ++j) val[j] = trig_poly_sin(red[j].r);
@@ -100,17 +109,25 @@ struct RowDirectTrig {
     }
 };
 template <>
-struct RowDirect<SinF, double, true> : RowDirectTrig<SinF> {};
+struct RowDirect<SinF, double, 1> : RowDirectTrig<SinF, false> {};
 template <>
-struct RowDirect<AccF, double, true> : RowDirectTrig<AccF> {};
+struct RowDirect<AccF, double, 1> : RowDirectTrig<AccF, false> {};
 template <>
-struct RowDirect<VelF, double, true> : RowDirectTrig<VelF> {};
+struct RowDirect<VelF, double, 1> : RowDirectTrig<VelF, false> {};
 template <>
-struct RowDirect<DisF, double, true> : RowDirectTrig<DisF> {};
+struct RowDirect<DisF, double, 1> : RowDirectTrig<DisF, false> {};
+template <>
+struct RowDirect<SinF, double, 2> : RowDirectTrig<SinF, true> {};
+template <>
+struct RowDirect<AccF, double, 2> : RowDirectTrig<AccF, true> {};
+template <>
+struct RowDirect<VelF, double, 2> : RowDirectTrig<VelF, true> {};
+template <>
+struct RowDirect<DisF, double, 2> : RowDirectTrig<DisF, true> {};
 
 // The table integrand in fp64: the row is a run of equally spaced samples, so when its two ends
 // share a table cell (nearly always) each sample is one fma (ProfileF::eval_run).
-template <bool FAST>
+template <int FAST>
 struct RowDirect<ProfileF, double, FAST> {
     static BQ_HD void eval(const ProfileF& f, double rowbase, const double (&col)[kCols], double h, double a,
                            double (&v)[kCols]) {
@@ -118,7 +135,7 @@ struct RowDirect<ProfileF, double, FAST> {
         const double x_last = fma(rowbase + col[kCols - 1], h, a);
         if (f.template eval_run<kCols>(x_first, x_last, v)) return;
 #pragma unroll
-        for (int j = 0; j < kCols; ++j) v[j] = point_direct<ProfileF, double, false>(f, rowbase, col[j], h, a);
+        for (int j = 0; j < kCols; ++j) v[j] = point_direct<ProfileF, double, 0>(f, rowbase, col[j], h, a);
     }
 };
 

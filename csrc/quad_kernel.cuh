@@ -263,7 +263,7 @@ struct PartWorker {
     }
 
     // DIRECT: adds every sample of `tile` into `acc`.  Only the globally last tile can be short.
-    template <bool FAST>
+    template <int FAST>
     __device__ __forceinline__ void tile_direct(uint64_t tile, TileAcc<R>& acc) const {
         TileGeom g;
         if (tile == last_tile) {
@@ -330,12 +330,15 @@ struct PartWorker {
                 buf ^= 1;
             }
         } else {
-            const bool fast = F::kTrig && (P.flags & kFlagFastTrig);   // uniform: a kernel parameter
+            // uniform: kernel parameters
+            const int fast = !(F::kTrig && (P.flags & kFlagFastTrig)) ? 0 : ((P.flags & kFlagRowK) ? 2 : 1);
             for (uint64_t t = lo64; t < hi64; ++t) {
-                if (fast)
-                    tile_direct<true>(t, acc);
+                if (fast == 2)
+                    tile_direct<2>(t, acc);
+                else if (fast == 1)
+                    tile_direct<1>(t, acc);
                 else
-                    tile_direct<false>(t, acc);
+                    tile_direct<0>(t, acc);
                 if (((t - lo64) & (kFlushTiles - 1)) == kFlushTiles - 1 || t + 1 == hi64) {
                     total = dd_acc_lazy(total, acc.flush());
                     acc.clear();

@@ -119,7 +119,9 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
     memset(&st, 0, sizeof(st));
     const ScanScratchLayout L = scan_scratch_layout(c->scan_tiles_cap);
     st.a_ll = reinterpret_cast<uint64_t*>(c->d_scan_scratch + L.a_off);
+    st.aex_ll = reinterpret_cast<uint64_t*>(c->d_scan_scratch + L.aex_off);
     st.gt_ll = reinterpret_cast<uint64_t*>(c->d_scan_scratch + L.gt_off);
+    st.head_ll = reinterpret_cast<uint64_t*>(c->d_scan_scratch + L.head_off);
     st.sgp_ll = reinterpret_cast<uint64_t*>(c->d_scan_scratch + L.sgp_off);
     st.segbase_ll = c->d_scan_misc;
     st.abort_word = c->d_scan_misc + 64;
@@ -129,6 +131,7 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
     st.comm = c->d_comm;
     for (int r = 0; r < BQ_MAX_WORLD; ++r) st.peers[r] = c->peers[r];
     st.peers[rank] = c->d_comm;
+    st.mc_comm = (c->use_nvls && world == c->world) ? c->mc_comm : nullptr;
     st.table = c->d_table;
     // Tables are indexed globally inside the kernel.  A replicating rank holds
     // the whole table; otherwise the buffer starts at this rank's slice.
@@ -141,6 +144,9 @@ static int scan_enqueue(bq_ctx* c, const bq_scan_job* job, int rank, int world, 
         st.peerP[r] = replicate ? c->scan_peerP[r] : nullptr;
         st.peerQ[r] = replicate ? c->scan_peerQ[r] : nullptr;
     }
+    const bool mc_tables = replicate && c->use_nvls && c->scan_mcP && c->scan_mcQ;
+    st.mcP = mc_tables ? c->scan_mcP : nullptr;
+    st.mcQ = mc_tables ? c->scan_mcQ : nullptr;
     uint64_t tiles = hp->tile_hi - hp->tile_lo;
     unsigned grid = unsigned(c->scan_grid);
     if (tiles < grid) grid = unsigned(tiles ? tiles : 1);
@@ -211,9 +217,13 @@ int bq_world_cumulative(bq_world* w, const bq_scan_job* job, double* const* dP, 
     if (!w || !job || !dP || !dQ) return BQ_ERR_INVALID;
     const int n = bq_world_size(w);
     if (job->replicate && n > 1) {
+        double* mcP = bq_world_table_multicast(w, dP[0]);
+        double* mcQ = bq_world_table_multicast(w, dQ[0]);
         for (int r = 0; r < n; ++r) {
             int rc = bq_ctx_set_scan_peers(bq_world_ctx(w, r), dP, dQ);
             if (rc != BQ_OK) return rc;
+            bq_world_ctx(w, r)->scan_mcP = mcP;     // null unless the tables came from bq_world_alloc_tables
+            bq_world_ctx(w, r)->scan_mcQ = mcQ;
         }
     }
     for (int r = 0; r < n; ++r) {

@@ -10,22 +10,24 @@
 //       group into the group total, the group totals into the supergroup prefix, and — for the
 //       last tile of a segment — store the segment total into every rank's comm block over
 //       NVLink                                            (replaces 4main.c:134-155, 200-219)
-//   B   read the few descriptors its exclusive prefix is made of (scan_plan.h: <= 31 tile
-//       aggregates, <= 31 group totals, one supergroup prefix, one segment base), re-evaluate
+//   B   read the three descriptors its exclusive prefix is made of (scan_plan.h: its prefix inside
+//       the group, the group's prefix inside the segment, the segment base), re-evaluate
 //       the tile, scan it and stream P and Q out in 256-bit stores — into every peer's table
 //       as well when replicate is on (the fused all-gather that replaces MPI_Bcast,
 //       4main.c:157,221)
 //
 // A descriptor is a few "LL" words — 32 bits of payload plus the 32-bit generation of the launch
 // per 8-byte word — so publishing is a plain store and waiting is polling the words themselves:
-// no fence, no flag, no counter, nothing to clear between calls.  A tile only ever waits for
-// EARLIER tiles, all of which are held by resident warps (cooperative launch), so the waits end.
+// no fence, no flag, no counter, nothing to clear between calls.  A and D only ever wait for A / D
+// of EARLIER tiles; B waits for A / D of tiles at most 1023 further on, which every warp has been
+// through before it starts that B (the A parts run ahead, see the tile loop); all warps are
+// resident (cooperative launch), so the waits end.
 //
-// One GPU runs A, D, B back to back per tile: a single pass, the evaluation of one tile overlapping
-// the stores of others.  With several GPUs a rank needs the lower ranks' segment totals before
-// its first store, so it runs A + D over all its tiles first and B afterwards; the prefix tree
-// is the same fixed shape either way, so the tables are bit-identical for every world size and
-// match cpu_scan.cpp bit for bit.
+// One GPU runs a single pass: A and D one round of the grid ahead of B, so the evaluation and the
+// prefix chain of the next round overlap the stores of this one.  With several GPUs a rank needs
+// the lower ranks' segment totals before its first store, so A + D cover the whole slice first.
+// The prefix tree is the same fixed shape either way, so the tables are bit-identical for every
+// world size and match cpu_scan.cpp bit for bit.
 //
 // A tile is 8 passes of 32 lanes x 8 samples.  The arithmetic tree of a tile (scan_core.cuh) is
 // that of a 256-thread block scan; one warp walks it pass by pass.
@@ -244,7 +246,8 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
         const TilePos tp = tile_pos(P, tile);
         if (tp.k != kScanGroup - 1 && !tp.last_in_seg) return;
 
-        // -- group duty: GT(g) = last element of the inclusive scan over the group's aggregates
+        // -- group duty: inclusive scan over the group's aggregates; every later tile of the group
+        //    gets its in-group prefix Ascan[k-1] as a descriptor, the group its total GT(g)
         Run r = run_identity();
         {
             double s = 0.0, w = 0.0;
@@ -258,12 +261,15 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
             if (lane < tp.k) r = run_from_tile(s, w, double(kScanTile));     // predecessors are full tiles
             if (lane == tp.k) r = run_from_tile(S, W, double(m));
         }
-        const Run gt = shfl_run(lanes_inclusive(r), tp.k);
+        const Run ainc = lanes_inclusive(r);
+        if (lane < tp.k) run_put<false>(st.aex_ll + 8 * (tile - P.tile_lo - tp.k + lane + 1), ainc, flag);
+        const Run gt = shfl_run(ainc, tp.k);
         const uint64_t gidx = P.seg_group0[tp.seg] - P.seg_group0[P.seg_lo] + tp.g;
         if (lane == 0) run_put<false>(st.gt_ll + 8 * gidx, gt, flag);
         if (tp.gi != kScanSuper - 1 && !tp.last_in_seg) return;
 
-        // -- supergroup duty: SGP(sg) = SGP(sg-1) (+) last element of the scan over its group totals
+        // -- supergroup duty: scan over its group totals; every group gets its in-segment prefix
+        //    head(g) = SGP(sg-1) (+) GTscan[gi-1], the supergroup its closing prefix SGP(sg)
         Run q = run_identity();
         {
             Run got = run_identity();
@@ -277,7 +283,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
             if (lane < tp.gi) q = got, q.cnt = double(kScanGroup) * double(kScanTile);   // predecessors are full groups
             if (lane == tp.gi) q = gt;
         }
-        const Run sgt = shfl_run(lanes_inclusive(q), tp.gi);
+        const Run ginc = lanes_inclusive(q);
         const uint64_t sgidx = P.seg_super0[tp.seg] - P.seg_super0[P.seg_lo] + tp.sg;
         Run prev = run_identity();
         if (tp.sg > 0) {
@@ -289,7 +295,13 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
             }
             prev.cnt = double(tp.sg) * double(kScanSuper) * double(kScanGroup) * double(kScanTile);
         }
-        const Run sgp = run_combine(prev, sgt);
+        {
+            Run gexcl = shfl_up_run(ginc, 1);
+            if (lane == 0) gexcl = run_identity();
+            const Run head = run_combine(prev, gexcl);
+            if (lane <= tp.gi) run_put<false>(st.head_ll + 8 * (gidx - tp.gi + lane), head, flag);
+        }
+        const Run sgp = run_combine(prev, shfl_run(ginc, tp.gi));
         if (lane == 0) run_put<false>(st.sgp_ll + 8 * sgidx, sgp, flag);
         if (!tp.last_in_seg) return;
 
@@ -303,7 +315,6 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
         const uint32_t m = scan_tile_count(P, tile);
         const TilePos tp = tile_pos(P, tile);
         const uint64_t gidx = P.seg_group0[tp.seg] - P.seg_group0[P.seg_lo] + tp.g;
-        const uint64_t sgidx = P.seg_super0[tp.seg] - P.seg_super0[P.seg_lo] + tp.sg;
         Run base = run_identity();
         if (tp.j == 0) {
             // first tile of a segment: segbase(s) = in-order fold of the totals of segments 0..s-1,
@@ -320,34 +331,24 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
             for (int s = 0; s < tp.seg; ++s) base = run_combine(base, shfl_run(mine, s));
             if (lane == 0) run_put<false>(st.segbase_ll + 8 * tp.seg, base, flag);
         }
-        // exclusive prefix of the tile: segbase (+) [(SGP(sg-1) (+) GTscan[gi-1]) (+) Ascan[k-1]]
+        // exclusive prefix of the tile: segbase (+) [head(g) (+) Ascan[k-1]] — three descriptors, written
+        // by the first tile of the segment and by the last tiles of the supergroup and of the group
         Run2 tile_excl;
         {
-            double s = 0.0, w = 0.0;
-            Run gt = run_identity(), prev = run_identity();
-            bool ok_a = lane >= tp.k, ok_g = lane >= tp.gi, ok_s = tp.sg == 0, ok_b = tp.j == 0;
-            const uint64_t* asrc = st.a_ll + 4 * (tile - P.tile_lo - tp.k + lane);
-            const uint64_t* gsrc = st.gt_ll + 8 * (gidx - tp.gi + lane);
+            Run aexcl = run_identity(), head = run_identity();
+            bool ok_a = tp.k == 0, ok_h = false, ok_b = tp.j == 0;
+            const uint64_t* asrc = st.aex_ll + 8 * (tile - P.tile_lo);
+            const uint64_t* hsrc = st.head_ll + 8 * gidx;
             wait.rearm();
             for (;;) {
-                if (!ok_a) ok_a = ptx::ll_get<false>(asrc, flag, s) && ptx::ll_get<false>(asrc + 2, flag, w);
-                if (!ok_g) ok_g = run_get<false>(gsrc, flag, gt);
-                if (!ok_s) ok_s = run_get<false>(st.sgp_ll + 8 * (sgidx - 1), flag, prev);
+                if (!ok_a) ok_a = run_get<false>(asrc, flag, aexcl);
+                if (!ok_h) ok_h = run_get<false>(hsrc, flag, head);
                 if (!ok_b) ok_b = run_get<false>(st.segbase_ll + 8 * tp.seg, flag, base);
-                if (wait.done(ok_a && ok_g && ok_s && ok_b)) break;
+                if (wait.done(ok_a && ok_h && ok_b)) break;
             }
-            Run a = run_identity();
-            if (lane < tp.k) a = run_from_tile(s, w, double(kScanTile));
-            const Run ainc = lanes_inclusive(a);
-            Run aexcl = shfl_run(ainc, tp.k > 0 ? tp.k - 1 : 0);
-            if (tp.k == 0) aexcl = run_identity();
-            Run gq = run_identity();
-            if (lane < tp.gi) gq = gt, gq.cnt = double(kScanGroup) * double(kScanTile);
-            const Run ginc = lanes_inclusive(gq);
-            Run gexcl = shfl_run(ginc, tp.gi > 0 ? tp.gi - 1 : 0);
-            if (tp.gi == 0) gexcl = run_identity();
-            prev.cnt = double(tp.sg) * double(kScanSuper) * double(kScanGroup) * double(kScanTile);
-            const Run pre = run_combine(run_combine(prev, gexcl), aexcl);
+            aexcl.cnt = double(tp.k) * double(kScanTile);
+            head.cnt = double(tp.g) * double(kScanGroup) * double(kScanTile);
+            const Run pre = run_combine(head, aexcl);
             tile_excl = scan_tile_exclusive(base, pre);
         }
         Run2 wpre{0.0, 0.0};   // fold of the passes before this one ("warps before mine")
@@ -411,10 +412,19 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
                         const int o = i * 128 + lane * 4;
                         const double4 pv = *reinterpret_cast<const double4*>(stage + o);
                         const double4 qv = *reinterpret_cast<const double4*>(stage + 32 * kScanItems + o);
-                        for (int r = 0; r < P.world; ++r) {
-                            if (r == P.rank) continue;
-                            ptx::st_f64x4(st.peerP[r] + pass0 + o, pv.x, pv.y, pv.z, pv.w);
-                            ptx::st_f64x4(st.peerQ[r] + pass0 + o, qv.x, qv.y, qv.z, qv.w);
+                        if (st.mcP) {
+                            // NVLS: one store per 16 bytes to the multicast address; the switch
+                            // writes every rank's copy (this one's too — harmless, same values)
+                            ptx::multimem_st_f64x2(st.mcP + pass0 + o, pv.x, pv.y);
+                            ptx::multimem_st_f64x2(st.mcP + pass0 + o + 2, pv.z, pv.w);
+                            ptx::multimem_st_f64x2(st.mcQ + pass0 + o, qv.x, qv.y);
+                            ptx::multimem_st_f64x2(st.mcQ + pass0 + o + 2, qv.z, qv.w);
+                        } else {
+                            for (int r = 0; r < P.world; ++r) {
+                                if (r == P.rank) continue;
+                                ptx::st_f64x4(st.peerP[r] + pass0 + o, pv.x, pv.y, pv.z, pv.w);
+                                ptx::st_f64x4(st.peerQ[r] + pass0 + o, qv.x, qv.y, qv.z, qv.w);
+                            }
                         }
                     }
                     __syncwarp();
@@ -459,15 +469,24 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
     };
 
     // ---- the tile loop -----------------------------------------------------------------------
-    // One GPU: a single pass, A + duties + B tile by tile.  Several GPUs: a rank's first store needs
-    // the lower ranks' segment totals, so all aggregates and duties come first, then all B parts.
-    const int sweeps = multi ? 2 : 1;
+    // A tile's B part reads descriptors that the LAST tiles of its group and supergroup write, up
+    // to 1023 tiles further on, so the A parts (and duties) run ahead of the B parts: by `ahead`
+    // rounds of the grid on one GPU (>= 1024 tiles, so every descriptor a B part waits for belongs
+    // to an A part that its warp has already been through — the waits always end — and the
+    // evaluation of the next round overlaps the stores of this one); by the whole slice with
+    // several GPUs, whose first store also needs the lower ranks' segment totals.
+    {
+        const uint64_t first = P.tile_lo + gwarp;
+        uint64_t ahead = (uint64_t(kScanGroup) * kScanSuper + nwarps - 1) / nwarps;
+        if (multi) ahead = (P.tile_hi - P.tile_lo + nwarps - 1) / nwarps + 1;
 #pragma unroll 1
-    for (int sweep = 0; sweep < sweeps; ++sweep) {
-#pragma unroll 1
-        for (uint64_t tile = P.tile_lo + gwarp; tile < P.tile_hi; tile += nwarps) {
-            if (!multi || sweep == 0) do_a(tile);
-            if (!multi || sweep == 1) do_b(tile);
+        for (uint64_t it = 0;; ++it) {
+            const uint64_t a_tile = first + it * nwarps;
+            if (a_tile < P.tile_hi) do_a(a_tile);
+            if (it < ahead) continue;
+            const uint64_t b_tile = first + (it - ahead) * nwarps;
+            if (b_tile >= P.tile_hi) break;
+            do_b(b_tile);
         }
     }
 

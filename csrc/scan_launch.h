@@ -13,7 +13,9 @@ namespace bq {
 // between calls, no fence or flag accompanies a descriptor, and readers poll the words themselves.
 struct ScanState {
     uint64_t* a_ll;           // [rank tiles][4]        tile aggregate (sum v, sum of local running sums)
-    uint64_t* gt_ll;          // [rank groups][8]       group total          (dd P, dd Q)
+    uint64_t* aex_ll;         // [rank tiles][8]        Ascan(g)[k-1]: prefix of the tile inside its group (dd P, dd Q)
+    uint64_t* gt_ll;          // [rank groups][8]       group total
+    uint64_t* head_ll;        // [rank groups][8]       SGP(sg-1) (+) GTscan(sg)[gi-1]: prefix of the group inside its segment
     uint64_t* sgp_ll;         // [rank supergroups][8]  in-segment prefix at the end of a supergroup
     uint64_t* segbase_ll;     // [kSegments][8]         exclusive prefix of each segment
     uint64_t* abort_word;     // a warp that timed out stores the generation here; everyone else stops waiting
@@ -33,9 +35,9 @@ struct ScanState {
     double* mcQ;
 };
 
-// Bytes of scratch a rank needs for `tiles` tiles (a_ll, gt_ll, sgp_ll in that order, 256-byte aligned parts).
+// Bytes of scratch a rank needs for `tiles` tiles (the five descriptor arrays, 256-byte aligned parts).
 struct ScanScratchLayout {
-    size_t a_off, gt_off, sgp_off, total;
+    size_t a_off, aex_off, gt_off, head_off, sgp_off, total;
 };
 constexpr size_t scan_up256(size_t v) { return (v + 255) & ~size_t(255); }
 constexpr ScanScratchLayout scan_scratch_layout(uint64_t tiles) {
@@ -43,8 +45,10 @@ constexpr ScanScratchLayout scan_scratch_layout(uint64_t tiles) {
     const uint64_t supers = groups / kScanSuper + kSegments + 1;
     ScanScratchLayout L{};
     L.a_off = 0;
-    L.gt_off = scan_up256(size_t(tiles) * 4 * sizeof(uint64_t));
-    L.sgp_off = L.gt_off + scan_up256(size_t(groups) * 8 * sizeof(uint64_t));
+    L.aex_off = scan_up256(size_t(tiles) * 4 * sizeof(uint64_t));
+    L.gt_off = L.aex_off + scan_up256(size_t(tiles) * 8 * sizeof(uint64_t));
+    L.head_off = L.gt_off + scan_up256(size_t(groups) * 8 * sizeof(uint64_t));
+    L.sgp_off = L.head_off + scan_up256(size_t(groups) * 8 * sizeof(uint64_t));
     L.total = L.sgp_off + scan_up256(size_t(supers) * 8 * sizeof(uint64_t));
     return L;
 }

@@ -279,6 +279,15 @@ int bq_ctx_export_comm(bq_ctx* ctx, unsigned char handle[BQ_IPC_HANDLE_BYTES]);
 /* ... and attach the other ranks' (handles[r] for r != rank; own slot ignored). */
 int bq_ctx_attach_peers(bq_ctx* ctx, int rank, int world,
                         const unsigned char* handles /* world * 64 bytes */);
+/* Alternative wiring for callers that already hold symmetric memory (e.g. a
+ * torch.distributed._symmetric_memory rendezvous): comm_ptrs[r] is rank r's block (>= 1 KiB,
+ * 256-byte aligned, `bytes` long) as mapped in THIS process, mc_ptr the NVLS multicast address of the
+ * same blocks or NULL.  The context uses comm_ptrs[rank] as its own block (and clears it): every
+ * rank must have returned from this call before the first collective call (host barrier). */
+int bq_ctx_adopt_comm(bq_ctx* ctx, int rank, int world, void* const* comm_ptrs, void* mc_ptr, size_t bytes);
+int bq_ctx_set_nvls(bq_ctx* ctx, int on);
+/* Multicast addresses of the replicated output tables of the next scans (NULL = peer stores). */
+int bq_ctx_set_scan_multicast(bq_ctx* ctx, double* mcP, double* mcQ);
 /* Zero this context's barrier state.  Every rank of a world must call it, and
  * the caller must make sure all have done so (host barrier) before the next
  * collective call; needed after a BQ_ERR_TIMEOUT. */
@@ -299,6 +308,18 @@ int bq_world_create(int ndev, const int* devices, bq_world** out);
 void bq_world_destroy(bq_world* w);
 int bq_world_size(const bq_world* w);
 bq_ctx* bq_world_ctx(bq_world* w, int rank);
+/* NVLS (NVSwitch multicast): a world whose comm blocks could be bound to a multicast object can
+ * publish with one multimem.st per word, fanned out by the switch, instead of one store per peer.
+ * Off by default (BQ_NVLS=1 in the environment turns it on at creation); same results either way. */
+int bq_world_has_multicast(const bq_world* w);
+int bq_world_set_nvls(bq_world* w, int on);
+/* Output tables of n doubles per rank in symmetric memory, bound to a multicast object when the
+ * fabric has one: a replicating bq_world_cumulative on them does its fused all-gather with
+ * multimem.st (when NVLS is on) instead of world-1 peer stores per datum.  P[r] / Q[r] receive
+ * rank r's table.  Freed by bq_world_free_tables or with the world. */
+int bq_world_alloc_tables(bq_world* w, uint64_t n, double** P, double** Q);
+void bq_world_free_tables(bq_world* w);
+double* bq_world_table_multicast(bq_world* w, const double* rank0_ptr);
 /* Launch on every device, wait for all; out[r] for each rank (may be NULL). */
 int bq_world_integrate(bq_world* w, const bq_job* job, bq_result* out);
 int bq_world_cumulative(bq_world* w, const bq_scan_job* job, double* const* dP, double* const* dQ,
