@@ -112,6 +112,12 @@ def _declare(lib, cuda):
     sig("bq_ctx_adopt_comm", i32, vp, i32, i32, P(vp), vp, C.c_size_t)
     sig("bq_ctx_set_nvls", i32, vp, i32)
     sig("bq_ctx_set_scan_multicast", i32, vp, vp, vp)
+    sig("bq_default_ctx", vp, i32)
+    sig("bq_default_world", vp, i32)
+    sig("bq_set_dist_ctx", i32, vp)
+    sig("bq_dist_ctx", vp)
+    sig("bq_ctx_world", i32, vp)
+    sig("bq_ctx_rank", i32, vp)
     sig("bq_world_has_multicast", i32, vp)
     sig("bq_world_set_nvls", i32, vp, i32)
     sig("bq_world_alloc_tables", i32, vp, u64, P(vp), P(vp))

@@ -146,23 +146,38 @@ def context(device=None):
             pass
     with _lock:
         if device not in _contexts:
-            _contexts[device] = Context(device)
+            # the process-wide context of the device (shared with the torch ops), not owned here
+            lib, cuda = _native.load()
+            if not cuda or lib.bq_cuda_device_count() == 0:
+                raise NativeError("no CUDA device available for a b200quad Context")
+            h = lib.bq_default_ctx(int(device))
+            if not h:
+                raise NativeError("bq_default_ctx(%d) failed: %s" % (device, _native.last_error()))
+            _contexts[device] = Context._wrap(lib, C.c_void_p(h), int(device), 0, 1)
         return _contexts[device]
 
 
 class LocalWorld:
     """`size` GPUs of this process; one launch per GPU, one host thread."""
 
-    def __init__(self, size, devices=None):
+    def __init__(self, size, devices=None, _shared=False):
         lib, cuda = _native.load()
         if not cuda:
             raise NativeError("LocalWorld needs the CUDA library")
         self.lib = lib
         self.size = int(size)
         devs = list(devices) if devices is not None else list(range(self.size))
-        arr = (C.c_int * self.size)(*devs)
-        h = C.c_void_p()
-        check(lib.bq_world_create(self.size, arr, C.byref(h)), "bq_world_create")
+        self._owned = not _shared
+        if _shared:
+            # the process-wide world of this size (devices 0..size-1), shared with the torch ops
+            h = lib.bq_default_world(self.size)
+            if not h:
+                raise NativeError("bq_default_world(%d) failed: %s" % (self.size, _native.last_error()))
+            h = C.c_void_p(h)
+        else:
+            arr = (C.c_int * self.size)(*devs)
+            h = C.c_void_p()
+            check(lib.bq_world_create(self.size, arr, C.byref(h)), "bq_world_create")
         self.handle = h
         self.devices = devs
         self.contexts = [Context._wrap(lib, C.c_void_p(lib.bq_world_ctx(h, r)), devs[r], r, self.size)
@@ -203,9 +218,9 @@ class LocalWorld:
         self.lib.bq_world_free_tables(self.handle)
 
     def close(self):
-        if self.handle:
+        if self.handle and self._owned:
             self.lib.bq_world_destroy(self.handle)
-            self.handle = None
+        self.handle = None
 
 
 def device_tensor(ptr, n, device):
@@ -220,7 +235,7 @@ def device_tensor(ptr, n, device):
 def local_world(size):
     with _lock:
         if size not in _local_worlds:
-            _local_worlds[size] = LocalWorld(size)
+            _local_worlds[size] = LocalWorld(size, _shared=True)
         return _local_worlds[size]
 
 
@@ -258,6 +273,7 @@ class DistWorld:
                   "bq_ctx_attach_peers")
             self.transport = "cuda-ipc"
         self.ctx.rank, self.ctx.world = self.rank, self.size
+        lib.bq_set_dist_ctx(self.ctx.handle)      # the torch ops' world > 1 path uses this context
         dist.barrier(group=group)
 
     def _symm_alloc(self, nbytes, device):

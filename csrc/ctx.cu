@@ -11,6 +11,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <vector>
 
 #include "ctx.h"
@@ -718,6 +719,55 @@ int bq_world_integrate(bq_world* w, const bq_job* job, bq_result* out) {
     }
     return worst;
 }
+
+}  // extern "C"
+
+// ---- process-wide defaults ------------------------------------------------------
+// One context per device and one world per size, created on first use and shared by everything
+// in the process that does not bring its own: the Python layer (parallel.context(),
+// parallel.local_world()) and the torch ops resolve to the SAME objects, so a table set through one
+// is the table the other integrates, and their calls are ordered against each other.
+namespace {
+std::mutex g_default_mu;
+bq_ctx* g_default_ctx[64] = {};
+bq_world* g_default_world[BQ_MAX_WORLD + 1] = {};
+bq_ctx* g_dist_ctx = nullptr;
+}  // namespace
+
+extern "C" {
+
+bq_ctx* bq_default_ctx(int device) {
+    if (device < 0 || device >= 64) {
+        set_error("bq_default_ctx: device %d out of range", device);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(g_default_mu);
+    if (!g_default_ctx[device] && bq_ctx_create(device, &g_default_ctx[device]) != BQ_OK) g_default_ctx[device] = nullptr;
+    return g_default_ctx[device];
+}
+
+bq_world* bq_default_world(int size) {
+    if (size < 1 || size > BQ_MAX_WORLD) {
+        set_error("bq_default_world: size %d out of range", size);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(g_default_mu);
+    if (!g_default_world[size] && bq_world_create(size, nullptr, &g_default_world[size]) != BQ_OK) g_default_world[size] = nullptr;
+    return g_default_world[size];
+}
+
+// The context of this process's rank in the torch.distributed world (registered by DistWorld).
+int bq_set_dist_ctx(bq_ctx* c) {
+    std::lock_guard<std::mutex> lock(g_default_mu);
+    g_dist_ctx = c;
+    return BQ_OK;
+}
+bq_ctx* bq_dist_ctx(void) {
+    std::lock_guard<std::mutex> lock(g_default_mu);
+    return g_dist_ctx;
+}
+int bq_ctx_world(const bq_ctx* c) { return c ? c->world : 0; }
+int bq_ctx_rank(const bq_ctx* c) { return c ? c->rank : -1; }
 
 }  // extern "C"
 

@@ -58,6 +58,12 @@ int bq_world_create(int, const int*, bq_world** out) {
 void bq_world_destroy(bq_world*) {}
 int bq_world_size(const bq_world*) { return 0; }
 bq_ctx* bq_world_ctx(bq_world*, int) { return nullptr; }
+bq_ctx* bq_default_ctx(int) { unsupported("bq_default_ctx"); return nullptr; }
+bq_world* bq_default_world(int) { unsupported("bq_default_world"); return nullptr; }
+int bq_set_dist_ctx(bq_ctx*) { return unsupported("bq_set_dist_ctx"); }
+bq_ctx* bq_dist_ctx(void) { return nullptr; }
+int bq_ctx_world(const bq_ctx*) { return 0; }
+int bq_ctx_rank(const bq_ctx*) { return -1; }
 int bq_world_has_multicast(const bq_world*) { return 0; }
 int bq_world_set_nvls(bq_world*, int) { return unsupported("bq_world_set_nvls"); }
 int bq_world_alloc_tables(bq_world*, uint64_t, double**, double**) { return unsupported("bq_world_alloc_tables"); }

@@ -325,6 +325,16 @@ int bq_world_integrate(bq_world* w, const bq_job* job, bq_result* out);
 int bq_world_cumulative(bq_world* w, const bq_scan_job* job, double* const* dP, double* const* dQ,
                         bq_scan_result* out);
 
+/* Process-wide defaults, created on first use and never destroyed: the context of a device, the
+ * single-process world of a size, and (set by the Python DistWorld) the context that is this
+ * process's rank of the torch.distributed world.  The Python layer and the torch ops share them. */
+bq_ctx* bq_default_ctx(int device);
+bq_world* bq_default_world(int size);
+int bq_set_dist_ctx(bq_ctx* ctx);
+bq_ctx* bq_dist_ctx(void);
+int bq_ctx_world(const bq_ctx* ctx);
+int bq_ctx_rank(const bq_ctx* ctx);
+
 /* Baseline comparator pieces (NOT the product path): the same kernel with the
  * cross-GPU stage disabled leaves its 8/world segment pairs in a device
  * buffer so an external all-reduce (NCCL) can finish the job. */
