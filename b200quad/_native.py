@@ -83,6 +83,8 @@ def _declare(lib, cuda):
     sig("bq_cpu_integrate_segments", i32, P(Job), i32, i32, i32, P(Result))
     sig("bq_fold_segments", i32, P(Job), P(dbl), P(dbl), P(Result))
     sig("bq_cpu_cumulative", i32, P(ScanJob), i32, vp, vp, vp, P(ScanResult))
+    sig("bq_cpu_scan_totals", i32, P(ScanJob), i32, i32, i32, P(dbl))
+    sig("bq_cpu_scan_finish", i32, P(ScanJob), i32, i32, i32, P(dbl), vp, vp, vp, P(ScanResult))
     if not cuda:
         return
     sig("bq_cuda_device_count", i32)

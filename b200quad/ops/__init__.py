@@ -209,6 +209,11 @@ def cumulative_integrate(f="profile", x0=0.0, dx=1.0e-4, n=18_000_000, world=Non
     be = backend or globals()["backend"]()
     dist, dsize, dbackend = _dist_state()
     lib, _ = _native.load()
+    if be == "cpu" and dist is not None and dsize > 1 and (world is None or int(world) == dsize):
+        # one CPU rank per process (gloo): every rank scans its segments, 32 doubles are exchanged
+        w = parallel.CpuWorld(threads=threads)
+        P, Q, S, res, sl = w.cumulative(job, want_samples=want_samples, replicate=replicate)
+        return CumulativeResult(P, Q, S, res, "cpu", dsize, sl)
     if be == "cpu":
         P = torch.empty(n, dtype=torch.float64)
         Q = torch.empty(n, dtype=torch.float64)

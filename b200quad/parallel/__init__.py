@@ -433,3 +433,77 @@ class CpuWorld:
         check(self.lib.bq_fold_segments(C.byref(job), hi, lo, C.byref(out)), "bq_fold_segments")
         out.world, out.rank = self.size, self.rank
         return out
+
+    def cumulative(self, job, want_samples=False, replicate=True):
+        """Running sums over the gloo ranks: every rank scans its own segments, ONE all_gather moves
+        the 8 segment totals (32 doubles), every rank finishes its slice with the right bases.  The
+        reference gathers whole slices to rank 0, fixes the carries there serially and broadcasts
+        144 MB (4main.c:141-157); here slices only travel when replicate=True asks for whole tables.
+        Returns (P, Q, samples or None, ScanResult, (lo, hi))."""
+        import torch
+        n = int(job.n)
+        res = ScanResult()
+        if self.size == 1:
+            P = torch.empty(n, dtype=torch.float64)
+            Q = torch.empty(n, dtype=torch.float64)
+            S = torch.empty(n, dtype=torch.float64) if want_samples else None
+            check(self.lib.bq_cpu_cumulative(C.byref(job), self.threads, C.c_void_p(P.data_ptr()),
+                                             C.c_void_p(Q.data_ptr()), C.c_void_p(S.data_ptr() if S is not None else 0),
+                                             C.byref(res)), "bq_cpu_cumulative")
+            return P, Q, S, res, (0, n)
+        threads = max(1, self.threads // self.size)
+        mine = torch.zeros(32, dtype=torch.float64)
+        buf = (C.c_double * 32)()
+        check(self.lib.bq_cpu_scan_totals(C.byref(job), self.rank, self.size, threads, buf), "bq_cpu_scan_totals")
+        mine[:] = torch.tensor(list(buf), dtype=torch.float64)
+        parts = [torch.zeros_like(mine) for _ in range(self.size)]
+        self.dist.all_gather(parts, mine, group=self.group)
+        segs = _native.SEGMENTS // self.size
+        allt = (C.c_double * 32)()
+        for r, t in enumerate(parts):
+            for k in range(4 * r * segs, 4 * (r + 1) * segs):
+                allt[k] = float(t[k])
+        tiles = (n + 2047) // 2048
+        lo = (self.rank * segs * tiles // 8) * 2048
+        hi = min(n, ((self.rank + 1) * segs * tiles // 8) * 2048)
+        m = max(hi - lo, 0)
+        P = torch.empty(max(m, 1), dtype=torch.float64)
+        Q = torch.empty(max(m, 1), dtype=torch.float64)
+        S = torch.empty(max(m, 1), dtype=torch.float64) if want_samples else None
+        check(self.lib.bq_cpu_scan_finish(C.byref(job), self.rank, self.size, threads, allt, C.c_void_p(P.data_ptr()),
+                                          C.c_void_p(Q.data_ptr()), C.c_void_p(S.data_ptr() if S is not None else 0),
+                                          C.byref(res)), "bq_cpu_scan_finish")
+        P, Q = P[:m], Q[:m]
+        S = S[:m] if S is not None else None
+        # the three scalars of the result live on the rank that holds the end of the grid: share them
+        fin = torch.tensor([res.p_last, res.q_last, res.p_second_last, 1.0 if hi == n and m > 0 else 0.0],
+                           dtype=torch.float64)
+        fins = [torch.zeros_like(fin) for _ in range(self.size)]
+        self.dist.all_gather(fins, fin, group=self.group)
+        owner = max(r for r, f in enumerate(fins) if float(f[3]) == 1.0)
+        res.p_last, res.q_last = float(fins[owner][0]), float(fins[owner][1])
+        res.p_second_last = float(fins[owner][2])
+        if n >= 2 and float(fins[owner][2]) == 0.0 and owner > 0:      # P[n-2] sits at the end of the previous slice
+            prev_last = torch.tensor([float(P[-1]) if m > 0 else 0.0], dtype=torch.float64)
+            lasts = [torch.zeros_like(prev_last) for _ in range(self.size)]
+            self.dist.all_gather(lasts, prev_last, group=self.group)
+            res.p_second_last = float(lasts[owner - 1][0])
+        if not replicate:
+            return P, Q, S, res, (lo, hi)
+        # whole tables everywhere (the MPI_Bcast semantics, 4main.c:157,221): rank by rank broadcast
+        fullP = torch.empty(n, dtype=torch.float64)
+        fullQ = torch.empty(n, dtype=torch.float64)
+        fullS = torch.empty(n, dtype=torch.float64) if want_samples else None
+        for r in range(self.size):
+            rlo = (r * segs * tiles // 8) * 2048
+            rhi = min(n, ((r + 1) * segs * tiles // 8) * 2048)
+            if rhi <= rlo:
+                continue
+            for full, part in ((fullP, P), (fullQ, Q), (fullS, S)):
+                if full is None:
+                    continue
+                if r == self.rank:
+                    full[rlo:rhi] = part
+                self.dist.broadcast(full[rlo:rhi], src=r if self.group is None else self.dist.get_global_rank(self.group, r),
+                                    group=self.group)
+        return fullP, fullQ, fullS, res, (0, n)

@@ -248,40 +248,89 @@ struct CpuScan {
     }
 };
 
+template <class F, class Fn>
+void parallel_tiles(const ScanPlan& P, int threads, Fn fn) {
+    std::atomic<uint64_t> next(P.tile_lo);
+    auto body = [&]() {
+        for (;;) {
+            const uint64_t t = next.fetch_add(1);
+            if (t >= P.tile_hi) break;
+            fn(t);
+        }
+    };
+    if (threads <= 1) {
+        body();
+    } else {
+        std::vector<std::thread> pool;
+        for (int i = 0; i < threads; ++i) pool.emplace_back(body);
+        for (auto& th : pool) th.join();
+    }
+}
+
+// Phase 1 of a rank: aggregates and prefix tree of its own segments; totals[s][4] = (P_hi, P_lo,
+// Q_hi, Q_lo) of every owned segment (what the kernel's segment duty stores into the comm blocks).
+template <class F>
+int run_scan_totals(const ScanPlan& P, const double* table, int threads, double* totals) {
+    CpuScan<F> S(P, table);
+    parallel_tiles<F>(P, threads, [&](uint64_t t) { S.tile_aggregate(t); });
+    for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s) {
+        S.segment_prefixes(int(s));
+        const Run& r = S.seg_tot[s];
+        totals[4 * s + 0] = r.p.hi, totals[4 * s + 1] = r.p.lo, totals[4 * s + 2] = r.q.hi, totals[4 * s + 3] = r.q.lo;
+    }
+    return BQ_OK;
+}
+
+// Phase 2: with every segment's total known (all ranks'), the bases and this rank's slice of the
+// tables.  Pout / Qout / Sout are indexed globally (the caller passes slice pointers shifted back).
+template <class F>
+int run_scan_finish(const ScanPlan& P, const double* table, int threads, const double* totals, double* Pout,
+                    double* Qout, double* Sout, bq_scan_result* out) {
+    CpuScan<F> S(P, table);
+    parallel_tiles<F>(P, threads, [&](uint64_t t) { S.tile_aggregate(t); });
+    for (uint32_t s = P.seg_lo; s < P.seg_hi; ++s) S.segment_prefixes(int(s));
+    for (int s = 0; s < kSegments; ++s) {
+        S.seg_tot[s].p = dd{totals[4 * s + 0], totals[4 * s + 1]};
+        S.seg_tot[s].q = dd{totals[4 * s + 2], totals[4 * s + 3]};
+    }
+    S.bases();
+    parallel_tiles<F>(P, threads, [&](uint64_t t) { S.tile_store(t, Pout, Qout, Sout); });
+    memset(out, 0, sizeof(*out));
+    out->slice_begin = P.tile_lo * uint64_t(kScanTile);
+    const uint64_t e = P.tile_hi * uint64_t(kScanTile);
+    out->slice_end = e < P.n ? e : P.n;
+    if (out->slice_end == P.n && out->slice_end > out->slice_begin) {
+        out->p_last = Pout[P.n - 1];
+        out->q_last = Qout[P.n - 1];
+        out->p_second_last = (P.n >= 2 && P.n - 2 >= out->slice_begin) ? Pout[P.n - 2] : 0.0;
+    }
+    out->world = P.world;
+    out->rank = P.rank;
+    out->status = BQ_OK;
+    return BQ_OK;
+}
+
 template <class F>
 int run_scan(const ScanPlan& P, const double* table, int threads, double* Pout, double* Qout,
              double* Sout, bq_scan_result* out) {
-    CpuScan<F> S(P, table);
-    auto parallel_tiles = [&](auto fn) {
-        std::atomic<uint64_t> next(0);
-        auto body = [&]() {
-            for (;;) {
-                const uint64_t t = next.fetch_add(1);
-                if (t >= P.n_tiles) break;
-                fn(t);
-            }
-        };
-        if (threads <= 1) {
-            body();
-        } else {
-            std::vector<std::thread> pool;
-            for (int i = 0; i < threads; ++i) pool.emplace_back(body);
-            for (auto& th : pool) th.join();
-        }
-    };
-    parallel_tiles([&](uint64_t t) { S.tile_aggregate(t); });
-    for (int s = 0; s < kSegments; ++s) S.segment_prefixes(s);
-    S.bases();
-    parallel_tiles([&](uint64_t t) { S.tile_store(t, Pout, Qout, Sout); });
-    memset(out, 0, sizeof(*out));
-    out->p_last = Pout[P.n - 1];
-    out->q_last = Qout[P.n - 1];
-    out->p_second_last = P.n >= 2 ? Pout[P.n - 2] : 0.0;
-    out->slice_begin = 0;
-    out->slice_end = P.n;
-    out->world = 1;
-    out->status = BQ_OK;
-    return BQ_OK;
+    double totals[4 * kSegments] = {};
+    int rc = run_scan_totals<F>(P, table, threads, totals);
+    if (rc != BQ_OK) return rc;
+    rc = run_scan_finish<F>(P, table, threads, totals, Pout, Qout, Sout, out);
+    if (rc == BQ_OK && P.n >= 2) out->p_second_last = Pout[P.n - 2];
+    return rc;
+}
+
+template <class Fn>
+int dispatch_scan(int integrand, Fn fn) {
+    switch (integrand) {
+        case BQ_F_SIN: return fn(SinF{});
+        case BQ_F_ACC: return fn(AccF{});
+        case BQ_F_VEL: return fn(VelF{});
+        case BQ_F_DIS: return fn(DisF{});
+        case BQ_F_PROFILE: return fn(ProfileF{});
+        default: return BQ_ERR_INVALID;
+    }
 }
 
 }  // namespace
@@ -304,4 +353,33 @@ extern "C" int bq_cpu_cumulative(const bq_scan_job* job, int threads, double* P,
         case BQ_F_PROFILE: return run_scan<ProfileF>(plan, table, threads, P, Q, samples, out);
         default: return BQ_ERR_INVALID;
     }
+}
+
+// ---- one rank of a multi-process CPU world (the gloo layout; capability of the per-rank scans +
+// root carry fix-up of 4main.c:90-160,178-221, without a root) ----------------------------------
+extern "C" int bq_cpu_scan_totals(const bq_scan_job* job, int rank, int world, int threads, double* totals) {
+    using namespace bq;
+    if (!job || !totals) return BQ_ERR_INVALID;
+    int len = 0;
+    const double* table = default_profile(&len);
+    ScanPlan plan;
+    const int rc = make_scan_plan(*job, rank, world, len, &plan);
+    if (rc != BQ_OK) return rc;
+    return dispatch_scan(plan.integrand, [&](auto f) { return run_scan_totals<decltype(f)>(plan, table, threads, totals); });
+}
+
+extern "C" int bq_cpu_scan_finish(const bq_scan_job* job, int rank, int world, int threads, const double* totals,
+                                  double* P_slice, double* Q_slice, double* samples_slice, bq_scan_result* out) {
+    using namespace bq;
+    if (!job || !totals || !P_slice || !Q_slice || !out) return BQ_ERR_INVALID;
+    int len = 0;
+    const double* table = default_profile(&len);
+    ScanPlan plan;
+    const int rc = make_scan_plan(*job, rank, world, len, &plan);
+    if (rc != BQ_OK) return rc;
+    const uint64_t shift = plan.tile_lo * uint64_t(kScanTile);     // the slice buffers start at this rank's first sample
+    return dispatch_scan(plan.integrand, [&](auto f) {
+        return run_scan_finish<decltype(f)>(plan, table, threads, totals, P_slice - shift, Q_slice - shift,
+                                            samples_slice ? samples_slice - shift : nullptr, out);
+    });
 }

@@ -141,15 +141,19 @@ int bq_cumulative_noalloc(int device, const bq_scan_job* job, double* dP, double
                   (unsigned long long)job->n, (unsigned long long)BQ_NOALLOC_MAX_SAMPLES);
         return BQ_ERR_INVALID;
     }
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev || device >= kMaxDevices) {
+    if (device < 0 || device >= kMaxDevices) {
+        set_error("bq_cumulative_noalloc: device %d not available", device);
+        return BQ_ERR_INVALID;
+    }
+    // Hot path of a latency-critical caller: no device-count query per call; a device that does
+    // not exist is reported by cudaSetDevice / the set-up below.
+    int prev = -1;
+    BQ_NA_CUDA(cudaGetDevice(&prev));
+    if (prev != device && cudaSetDevice(device) != cudaSuccess) {
         cudaGetLastError();
         set_error("bq_cumulative_noalloc: device %d not available", device);
         return BQ_ERR_INVALID;
     }
-    int prev = -1;
-    BQ_NA_CUDA(cudaGetDevice(&prev));
-    if (prev != device) BQ_NA_CUDA(cudaSetDevice(device));
     struct Restore {
         int prev, device;
         ~Restore() {

@@ -190,6 +190,15 @@ int bq_fold_segments(const bq_job* job, const double* seg_hi, const double* seg_
 int bq_cpu_cumulative(const bq_scan_job* job, int threads, double* P, double* Q, double* samples,
                       bq_scan_result* out);
 
+/* One rank of a multi-process CPU world (gloo layout).  Phase 1: totals[4*s .. 4*s+3] = (P_hi, P_lo,
+ * Q_hi, Q_lo) of every segment s this rank owns (rank r of world W owns 8/W consecutive segments);
+ * the caller gathers the 8 totals from all ranks (the only communication: 32 doubles, where the
+ * reference gathers whole slices to its root, 4main.c:141-155); phase 2 writes this rank's slice
+ * [out->slice_begin, out->slice_end) of the tables into buffers that start at the slice. */
+int bq_cpu_scan_totals(const bq_scan_job* job, int rank, int world, int threads, double* totals /* 32 */);
+int bq_cpu_scan_finish(const bq_scan_job* job, int rank, int world, int threads, const double* totals,
+                       double* P_slice, double* Q_slice, double* samples_slice, bq_scan_result* out);
+
 /* ---- CUDA contexts ----------------------------------------------------- */
 
 typedef struct bq_ctx bq_ctx;
@@ -250,14 +259,16 @@ int bq_ctx_reserve_scan(bq_ctx* ctx, uint64_t n);
  * buffers, processes so close to the memory limit that an allocation may fail.
  * Same fused kernel and same results as bq_cumulative on one GPU, but its
  * scratch is a fixed static device array compiled into the library (about
- * 1.6 MB per GPU, held until the process exits), so:
+ * 3.3 MB per GPU, held until the process exits), so:
  *   - n must not exceed BQ_NOALLOC_MAX_SAMPLES (larger n is rejected with
  *     BQ_ERR_INVALID and a message; use bq_cumulative instead);
  *   - the first call on a device does that device's one-time set-up
  *     (synchronous runtime calls): make it before any stream capture begins;
  *   - every call on a device shares the array: calls that overlap on the GPU
  *     race, so issue them on one stream (or otherwise serialise them);
- *   - single GPU only; job->replicate and job->want_samples are ignored.
+ *   - single GPU only; job->replicate and job->want_samples are ignored;
+ *   - the PROFILE integrand is always the library's default table (ex4vel.h): a table set with
+ *     bq_ctx_set_profile belongs to a context, and this entry point has none.
  * The caller passes the inputs (job) and the outputs: P and Q (device memory,
  * n doubles each, 32-byte aligned) and, optionally, `out` (device or pinned
  * host memory) which receives the result block.  Work is enqueued on `stream`

@@ -11,6 +11,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SCAN_N = 300_001
 
 
 def _free_port():
@@ -30,7 +31,12 @@ def _worker(rank, world, port, n, expected, q):
     import b200quad as bq
     r = bq.integrate_result("sin", 0.0, math.pi, n, "left", backend="cpu", threads=2)
     p = bq.integrate("profile", 0.0, 1800.0, 180_000, "trap", backend="cpu", threads=2)
-    q.put((rank, r.value, r.value_lo, r.world, p))
+    # the distributed scan of 4main.c:90-221: whole tables everywhere, then slices only
+    c = bq.cumulative_integrate("profile", 0.0, 1800.0 / SCAN_N, SCAN_N, replicate=True, backend="cpu", threads=2)
+    s = bq.cumulative_integrate("vel", 0.0, 1800.0 / SCAN_N, SCAN_N, replicate=False, backend="cpu", threads=2)
+    scan = (float(c.P.sum()), float(c.Q.sum()), c.p_last, c.q_last, c.p_second_last, tuple(c.P.shape),
+            s.slice, float(s.P.sum()), s.p_last, s.p_second_last, c.world)
+    q.put((rank, r.value, r.value_lo, r.world, p, scan))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -41,6 +47,8 @@ def test_gloo_world_matches_single_process(world):
     n = 3_000_017
     one = bq.integrate_result("sin", 0.0, math.pi, n, "left", backend="cpu")
     prof = bq.integrate("profile", 0.0, 1800.0, 180_000, "trap", backend="cpu")
+    c1 = bq.cumulative_integrate("profile", 0.0, 1800.0 / SCAN_N, SCAN_N, backend="cpu")
+    s1 = bq.cumulative_integrate("vel", 0.0, 1800.0 / SCAN_N, SCAN_N, backend="cpu")
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
@@ -51,7 +59,11 @@ def test_gloo_world_matches_single_process(world):
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, v, lo, w, pv in got:
+    for rank, v, lo, w, pv, scan in got:
         assert w == world
         assert v == one.value and lo == one.value_lo       # bit-identical on every rank
         assert pv == prof
+        psum, qsum, pl, ql, p2, shape, sl, spsum, spl, sp2, cw = scan
+        assert cw == world and shape == (SCAN_N,)
+        assert (psum, qsum, pl, ql, p2) == (float(c1.P.sum()), float(c1.Q.sum()), c1.p_last, c1.q_last, c1.p_second_last)
+        assert spsum == float(s1.P[sl[0]:sl[1]].sum()) and (spl, sp2) == (s1.p_last, s1.p_second_last)

@@ -76,3 +76,16 @@ def test_sizes_beyond_the_static_scratch_are_rejected():
                                    C.c_void_p(buf.data_ptr()), None, None)
     assert rc == 1                                                    # BQ_ERR_INVALID
     assert "exceeds the no-allocation limit" in _native.last_error()
+
+
+def test_a_grid_of_exactly_the_limit_runs():
+    """n equal to BQ_NOALLOC_MAX_SAMPLES uses the last descriptor of the static scratch."""
+    lib, _ = _native.load()
+    n = int(lib.bq_noalloc_max_samples())
+    dx = 1800.0 / n
+    P, Q, res = _call_noalloc(lib, n, dx)
+    assert res.status == 0 and (res.slice_begin, res.slice_end) == (0, n)
+    assert res.p_last == float(P[-1]) and res.q_last == float(Q[-1]) and res.p_second_last == float(P[-2])
+    assert abs(res.p_last * dx - 122000.004) < 1e-6
+    ref = bq.cumulative_integrate("profile", 0.0, dx, n, backend="cuda")
+    assert torch.equal(P, ref.P) and torch.equal(Q, ref.Q)
