@@ -81,6 +81,17 @@ def _dist_state():
     return None, 1, None
 
 
+_fast_jobs = {}
+
+
+def _dist_initialised():
+    try:
+        import torch.distributed as dist
+        return dist.is_available() and dist.is_initialized()
+    except Exception:
+        return False
+
+
 def _callable_integrate(fn, a, b, n, rule, dtype, chunk=1 << 22):
     """Slow path for arbitrary Python callables: chunked torch evaluation, Neumaier across chunks."""
     import torch
@@ -151,6 +162,14 @@ def integrate(f, a, b, n, rule="left", world=None, *, dtype="fp64", eval="auto",
     eval   'auto' | 'direct' | 'rotate'
     Returns a Python float; every rank of the world gets the same bits.
     """
+    # Repeated calls with the same arguments (a solver loop, a benchmark) skip the argument
+    # normalisation: the prepared job and its context are remembered per argument tuple.
+    key = None
+    if isinstance(f, str) and params is None:
+        key = (f, a, b, n, rule, world, dtype, eval, backend, _dist_initialised())
+        hit = _fast_jobs.get(key)
+        if hit is not None:
+            return hit[0].integrate_value(hit[1])
     integ, fn = models.get(f)
     if integ is None:
         return _callable_integrate(fn, float(a), float(b), int(n), rule, dtype)
@@ -165,7 +184,12 @@ def integrate(f, a, b, n, rule="left", world=None, *, dtype="fp64", eval="auto",
         elif world is None or int(world) == 1:
             ctx = parallel.context()
         if ctx is not None:
-            return ctx.integrate_value(make_job(integ, a, b, n, rule, dtype, eval, params))
+            job = make_job(integ, a, b, n, rule, dtype, eval, params)
+            if key is not None:
+                if len(_fast_jobs) > 256:
+                    _fast_jobs.clear()
+                _fast_jobs[key] = (ctx, job)
+            return ctx.integrate_value(job)
     return integrate_result(integ, a, b, n, rule, world, dtype=dtype, eval=eval, backend=backend,
                             params=params, threads=threads).value
 

@@ -221,7 +221,7 @@ def bench_integrate(args, env):
         e2e_value_last = bq.integrate(args.integrand, a, b, n, args.rule, **kw)
         e2e_s += time.perf_counter() - t0
         env.flush.zero_()
-        torch.cuda.synchronize(env.dev)
+        env.barrier()          # untimed: L2 flushed and the ranks level before the next call
     env.barrier()
     clocks = sampler.stop() if sampler else None
     last = bq.integrate_result(args.integrand, a, b, n, args.rule, **kw)

@@ -44,6 +44,13 @@ bq_ctx* dist_ctx_for(int64_t world) {
     return nullptr;
 }
 
+// torch's default stream is the NULL handle, which the C ABI reads as "the context's own stream":
+// name it explicitly so the work is ordered with everything else torch does on that stream.
+cudaStream_t current_stream(int device) {
+    cudaStream_t s = c10::cuda::getCurrentCUDAStream(static_cast<c10::DeviceIndex>(device));
+    return s ? s : cudaStreamLegacy;
+}
+
 bq_job make_job(int64_t integrand, double a, double b, int64_t n, int64_t rule, int64_t dtype,
                 int64_t eval, at::ArrayRef<double> params) {
     bq_job j{};
@@ -75,7 +82,7 @@ at::Tensor integrate_op(int64_t integrand, double a, double b, int64_t n, int64_
             // in-kernel NVLink combine leaves the same bits in every rank's output tensor
             const int dev = bq_ctx_device(dc);
             c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(dev));
-            cudaStream_t stream = c10::cuda::getCurrentCUDAStream(static_cast<c10::DeviceIndex>(dev));
+            cudaStream_t stream = current_stream(dev);
             at::Tensor out = at::empty({}, at::dtype(at::kDouble).device(at::kCUDA, dev));
             const int rc = bq_integrate_device_async(dc, &job, out.data_ptr<double>(), stream);
             TORCH_CHECK(rc == BQ_OK, "b200quad: ", bq_last_error());
@@ -91,7 +98,7 @@ at::Tensor integrate_op(int64_t integrand, double a, double b, int64_t n, int64_
     }
     c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(device));
     bq_ctx* c = ctx_for(int(device));
-    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(static_cast<c10::DeviceIndex>(device));
+    cudaStream_t stream = current_stream(int(device));
     // ONE kernel: it stores the integral straight into the output tensor.
     at::Tensor out = at::empty({}, at::dtype(at::kDouble).device(at::kCUDA, device));
     const int rc = bq_integrate_device_async(c, &job, out.data_ptr<double>(), stream);
@@ -128,7 +135,7 @@ std::tuple<at::Tensor, at::Tensor> cumulative_op(int64_t integrand, double x0, d
         const int64_t lo = (rank * segs * tiles / 8) * 2048;
         const int64_t hi = std::min<int64_t>(n, ((rank + 1) * segs * tiles / 8) * 2048);
         c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(dev));
-        cudaStream_t stream = c10::cuda::getCurrentCUDAStream(static_cast<c10::DeviceIndex>(dev));
+        cudaStream_t stream = current_stream(dev);
         at::Tensor P = at::empty({hi - lo}, at::dtype(at::kDouble).device(at::kCUDA, dev));
         at::Tensor Q = at::empty({hi - lo}, at::dtype(at::kDouble).device(at::kCUDA, dev));
         const int rc = bq_cumulative_async(dc, &job, P.data_ptr<double>(), Q.data_ptr<double>(), nullptr, stream);
@@ -137,7 +144,7 @@ std::tuple<at::Tensor, at::Tensor> cumulative_op(int64_t integrand, double x0, d
     }
     c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(device));
     bq_ctx* c = ctx_for(int(device));
-    cudaStream_t stream = c10::cuda::getCurrentCUDAStream(static_cast<c10::DeviceIndex>(device));
+    cudaStream_t stream = current_stream(int(device));
     at::Tensor P = at::empty({n}, at::dtype(at::kDouble).device(at::kCUDA, device));
     at::Tensor Q = at::empty({n}, at::dtype(at::kDouble).device(at::kCUDA, device));
     const int rc = bq_cumulative_async(c, &job, P.data_ptr<double>(), Q.data_ptr<double>(), nullptr,

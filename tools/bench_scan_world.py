@@ -12,8 +12,6 @@ import b200quad as bq
 world = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 for n in (18_000_000, 1 << 28):
     for replicate in (False, True):
-        if replicate and n > (1 << 27) and world > 4:
-            continue   # 8 full copies of 2 x 2 GiB tables: skip, the 18e6 case shows the path
         best = 1e9
         for it in range(5):
             r = bq.cumulative_integrate("profile", 0.0, 1800.0 / n, n, world=world, replicate=replicate,
