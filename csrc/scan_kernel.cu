@@ -42,6 +42,10 @@
 #include "scan_core.cuh"
 #include "scan_launch.h"
 
+#ifndef BQ_SCAN_MIN_CTAS
+#define BQ_SCAN_MIN_CTAS 2      // resident CTAs per SM the register budget is set for (2 -> 128 registers)
+#endif
+
 namespace bq {
 
 namespace {
@@ -165,7 +169,7 @@ __device__ __forceinline__ TilePos tile_pos(const ScanPlan& P, uint64_t tile) {
 // REPL = the fused all-gather (replicate) is compiled in; a separate instantiation so the
 // single-GPU / slice-only kernel carries none of its registers or staging.
 template <class F, bool REPL>
-__global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_constant__ ScanParams prm) {
+__global__ void __launch_bounds__(kScanThreads, BQ_SCAN_MIN_CTAS) scan_kernel(const __grid_constant__ ScanParams prm) {
     const ScanPlan& P = prm.P;
     const ScanState& st = prm.st;
     __shared__ ScanSmem sm;
@@ -201,7 +205,8 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
     const bool replicate = REPL && multi && (P.flags & kScanReplicate);
     extern __shared__ __align__(32) double sStage[];   // replicate only: [warp][P 256 | Q 256]
     double* const stage = sStage + warp * (2 * 32 * kScanItems);
-    Waiter wait(st.abort_word, gen, limit);
+    // (a Waiter is built where it is used: nothing of it stays live across the tile loop; a time-out
+    // is remembered in the abort word, not in a register)
 
     // Totals of owned segments that hold no tile (tiny n): nobody's duty, published up front.
     if (gwarp == 0 && lane < P.world && !(P.flags & kScanSkipPublish)) {
@@ -212,6 +217,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
 
     // ---- A + duties of one tile ------------------------------------------------------------
     auto do_a = [&](uint64_t tile) {
+        Waiter wait(st.abort_word, gen, limit);
         const uint32_t m = scan_tile_count(P, tile);
         // pass j = the samples of "warp j" of a block scan; each lane folds its 8 pass
         // shares in the order ((0+4)+(2+6)) + ((1+5)+(3+7)), the 32 lanes then meet in
@@ -312,6 +318,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
 
     // ---- B of one tile: prefix from descriptors, scan, store ----------------------------------
     auto do_b = [&](uint64_t tile) {
+        Waiter wait(st.abort_word, gen, limit);
         const uint32_t m = scan_tile_count(P, tile);
         const TilePos tp = tile_pos(P, tile);
         const uint64_t gidx = P.seg_group0[tp.seg] - P.seg_group0[P.seg_lo] + tp.g;
@@ -501,6 +508,7 @@ __global__ void __launch_bounds__(kScanThreads, 2) scan_kernel(const __grid_cons
     __syncthreads();
     if (!sm.is_last || warp != 0) return;
     if (multi) ptx::fence_sys(); else __threadfence();
+    Waiter wait(st.abort_word, gen, limit);
     if (replicate) {
         // Fused all-gather: every rank tells every rank "my stores into your tables are complete"
         // (a release store after the system fence above) and waits for the same word from everyone;
@@ -614,7 +622,7 @@ int scan_max_grid(int /*device*/, int sm_count) {
     int occ = occupancy_f<ProfileF>();
     const int o2 = occupancy_f<DisF>();
     if (o2 < occ) occ = o2;
-    if (occ > 2) occ = 2;
+    if (occ > BQ_SCAN_MIN_CTAS) occ = BQ_SCAN_MIN_CTAS;
     return occ * sm_count;
 }
 

@@ -45,8 +45,14 @@ def _worker(rank, world, port, n, q):
     for ns in SMALL_N:
         cs = bq.cumulative_integrate(n=ns, dx=1800.0 / ns, replicate=True)
         small.append((float(cs.P.sum()), float(cs.Q.sum()), float(cs.P[-1]), float(cs.Q[ns // 2])))
+    # the torch op with the world size as an input (riemann.cpp:63-65): this rank's kernel of the
+    # collective call, on torch's current stream, every rank's tensor holding the same bits
+    from b200quad.ops import torch_ops
+    t = torch_ops.integrate("sin", 0.0, math.pi, n, world=world)
+    tP, tQ = torch_ops.cumulative("profile", 0.0, 6e-4, 3_000_000, world=world)
+    op = (float(t), t.device.index, tuple(tP.shape), float(tP.sum()))
     q.put((rank, vals, c.p_last, c.p_second_last, float(c.P.sum()), float(c.Q[-1]), c2.slice,
-           float(c2.P.sum()), small))
+           float(c2.P.sum()), small, op))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -74,8 +80,10 @@ def test_torchrun_layout(world):
         p.join(timeout=120)
         assert p.exitcode == 0
     total_slice = 0.0
-    for rank, vals, p_last, p2, psum, qlast, sl, p2sum, small in got:
+    for rank, vals, p_last, p2, psum, qlast, sl, p2sum, small, op in got:
         assert small == small1
+        assert op[0] == one.value and op[1] == rank                  # torch op, world = the process group
+        assert op[2] == (sl[1] - sl[0],) and op[3] == p2sum          # its cumulative returns this rank's slice
         for v, lo, status, w in vals:
             assert status == 0 and w == world
             assert (v, lo) == (one.value, one.value_lo)
