@@ -59,6 +59,13 @@ int make_scan_plan(const bq_scan_job& job, int rank, int world, int table_len, S
     P->rank = rank;
     P->world = world;
     P->flags = (job.replicate ? kScanReplicate : 0u) | (job.want_samples ? kScanSamples : 0u);
+    if (job.integrand == BQ_F_SIN || job.integrand == BQ_F_ACC || job.integrand == BQ_F_VEL || job.integrand == BQ_F_DIS) {
+        // trig integrands: the bounded-argument sin/cos applies when the whole grid stays inside its range
+        const double w = job.integrand == BQ_F_SIN ? 1.0 : 1.0 / fabs(P->p[0]);
+        const double xl = job.x0 + double(job.n) * job.dx;
+        const double amax = fabs(job.x0) > fabs(xl) ? fabs(job.x0) : fabs(xl);
+        if (w * amax <= kFastTrigMax) P->flags |= kScanFastTrig;
+    }
     P->timeout_ms = 2000;
     P->n_tiles = (job.n + kScanTile - 1) / kScanTile;
     for (int s = 0; s <= kSegments; ++s) P->seg_tile[s] = (uint64_t(s) * P->n_tiles) / kSegments;

@@ -103,9 +103,11 @@ BQ_HD void scan_thread_values(const F& f, const ScanPlan& P, uint64_t first_idx,
         for (int j = 0; j < kScanItems; ++j) v[j] = f.template eval<double>(fma(base + double(j), P.dx, P.x0));
     } else {
 #pragma unroll
+        const bool fast = F::kTrig && (P.flags & kScanFastTrig);
+#pragma unroll
         for (int j = 0; j < kScanItems; ++j) {
             const double x = fma(base + double(j), P.dx, P.x0);
-            v[j] = (k0 + uint32_t(j) < m) ? f.template eval<double>(x) : 0.0;
+            v[j] = (k0 + uint32_t(j) < m) ? (fast ? f.template eval_fast<double>(x) : f.template eval<double>(x)) : 0.0;
         }
     }
 }

@@ -41,6 +41,7 @@ enum ScanFlags : uint32_t {
     kScanReplicate = 1u,
     kScanSamples = 2u,
     kScanSkipPublish = 4u,
+    kScanFastTrig = 8u,       // |angle| <= kFastTrigMax over the whole grid: bounded sin/cos (integrands.cuh)
 };
 
 struct ScanPlan {
