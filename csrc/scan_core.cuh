@@ -99,10 +99,14 @@ BQ_HD void scan_thread_values(const F& f, const ScanPlan& P, uint64_t first_idx,
         // The whole run lies inside the grid (every run but those of the last tile):
         // straight-line code, so the kScanItems evaluations overlap.  A per-sample
         // guard here turns into one branch per sample and serialises them.
+        if (F::kTrig && (P.flags & kScanFastTrig)) {     // uniform: a kernel parameter
+#pragma unroll
+            for (int j = 0; j < kScanItems; ++j) v[j] = f.template eval_fast<double>(fma(base + double(j), P.dx, P.x0));
+            return;
+        }
 #pragma unroll
         for (int j = 0; j < kScanItems; ++j) v[j] = f.template eval<double>(fma(base + double(j), P.dx, P.x0));
     } else {
-#pragma unroll
         const bool fast = F::kTrig && (P.flags & kScanFastTrig);
 #pragma unroll
         for (int j = 0; j < kScanItems; ++j) {
