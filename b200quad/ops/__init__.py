@@ -260,16 +260,23 @@ def cumulative_integrate(f="profile", x0=0.0, dx=1.0e-4, n=18_000_000, world=Non
             Q = torch.empty(n, dtype=torch.float64, device=dev)
             opened = dw.share_tables(P, Q)
         else:
-            P = torch.empty(hi - lo, dtype=torch.float64, device=dev)
-            Q = torch.empty(hi - lo, dtype=torch.float64, device=dev)
+            # a rank whose segments hold no tile (tiny n, many ranks) still takes part in the call:
+            # it gets a valid, empty slice
+            # (torch reports a null data_ptr for an empty view: the kernel gets the base buffer's address)
+            m = max(hi - lo, 0)
+            P = torch.empty(max(m, 4), dtype=torch.float64, device=dev)
+            Q = torch.empty(max(m, 4), dtype=torch.float64, device=dev)
             opened = None
         S = None
         if want_samples:
-            S = torch.empty(n if replicate else hi - lo, dtype=torch.float64, device=dev)
+            S = torch.empty(max(n if replicate else hi - lo, 4), dtype=torch.float64, device=dev)
         torch.cuda.synchronize(dev)
         res = ctx.cumulative(job, P.data_ptr(), Q.data_ptr(), S.data_ptr() if S is not None else 0)
         if opened is not None:
             dw.release_tables(opened)
+        if not replicate:
+            m = max(hi - lo, 0)
+            P, Q, S = P[:m], Q[:m], (S[:m] if S is not None else None)
         return CumulativeResult(P, Q, S, res, "cuda", dsize, (0, n) if replicate else (lo, hi))
 
     w = 1 if world is None else int(world)
@@ -290,13 +297,16 @@ def cumulative_integrate(f="profile", x0=0.0, dx=1.0e-4, n=18_000_000, world=Non
         dev = torch.device("cuda", lw.devices[r])
         lo = (r * (8 // w) * tiles // 8) * 2048
         hi = min(n, (((r + 1) * (8 // w)) * tiles // 8) * 2048)
-        m = n if replicate else hi - lo
-        Ps.append(torch.empty(m, dtype=torch.float64, device=dev))
-        Qs.append(torch.empty(m, dtype=torch.float64, device=dev))
+        m = n if replicate else max(hi - lo, 0)      # an empty slice is still a valid buffer (tiny n, many ranks)
+        # (torch reports a null data_ptr for an empty view: the kernel gets the base buffer's address)
+        Ps.append(torch.empty(max(m, 4), dtype=torch.float64, device=dev))
+        Qs.append(torch.empty(max(m, 4), dtype=torch.float64, device=dev))
         slices.append((0, n) if replicate else (lo, hi))
     for r in range(w):
         torch.cuda.synchronize(torch.device("cuda", lw.devices[r]))
     out = lw.cumulative(job, [p.data_ptr() for p in Ps], [q.data_ptr() for q in Qs])
+    Ps = [p[:hi_ - lo_] for p, (lo_, hi_) in zip(Ps, slices)]
+    Qs = [q[:hi_ - lo_] for q, (lo_, hi_) in zip(Qs, slices)]
     result = CumulativeResult(Ps[0], Qs[0], None, out[w - 1], "cuda", w, slices[0])
     result.all_P, result.all_Q, result.slices, result.per_rank = Ps, Qs, slices, out
     result.device_ms = max(float(o.device_ms) for o in out)

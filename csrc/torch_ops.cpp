@@ -136,11 +136,14 @@ std::tuple<at::Tensor, at::Tensor> cumulative_op(int64_t integrand, double x0, d
         const int64_t hi = std::min<int64_t>(n, ((rank + 1) * segs * tiles / 8) * 2048);
         c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(dev));
         cudaStream_t stream = current_stream(dev);
-        at::Tensor P = at::empty({hi - lo}, at::dtype(at::kDouble).device(at::kCUDA, dev));
-        at::Tensor Q = at::empty({hi - lo}, at::dtype(at::kDouble).device(at::kCUDA, dev));
+        // a rank whose segments hold no tile (tiny n) still takes part: a valid, empty slice
+        const int64_t m = std::max<int64_t>(hi - lo, 0);
+        // (the kernel gets the base buffers: an empty view has no address)
+        at::Tensor P = at::empty({std::max<int64_t>(m, 4)}, at::dtype(at::kDouble).device(at::kCUDA, dev));
+        at::Tensor Q = at::empty({std::max<int64_t>(m, 4)}, at::dtype(at::kDouble).device(at::kCUDA, dev));
         const int rc = bq_cumulative_async(dc, &job, P.data_ptr<double>(), Q.data_ptr<double>(), nullptr, stream);
         TORCH_CHECK(rc == BQ_OK, "b200quad: ", bq_last_error());
-        return {P, Q};
+        return {P.narrow(0, 0, m), Q.narrow(0, 0, m)};
     }
     c10::cuda::CUDAGuard guard(static_cast<c10::DeviceIndex>(device));
     bq_ctx* c = ctx_for(int(device));

@@ -214,3 +214,20 @@ def test_scan_peer_timeout_is_reported_not_hung():
             c.set_timeout_ms(2000)
     r = bq.cumulative_integrate("profile", 0.0, 1e-3, 1_800_000, world=2, replicate=False, backend="cuda")
     assert all(o.status == 0 for o in r.per_rank)
+
+
+@pytest.mark.parametrize("n", [1, 1000, 2048, 2049, 4097])
+def test_scan_with_ranks_that_own_no_tile(n):
+    """Tiny grids on several GPUs: some ranks' segments hold no tile; they still take part in the call
+    (empty slice, their segment totals are published as zero) and every rank reports the right scalars."""
+    if gpu_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    one = bq.cumulative_integrate("profile", 0.0, 1800.0 / max(n, 2), n, backend="cuda")
+    for world in _world_sizes():
+        for replicate in (False, True):
+            r = bq.cumulative_integrate("profile", 0.0, 1800.0 / max(n, 2), n, world=world, replicate=replicate,
+                                        backend="cuda")
+            for rank, o in enumerate(r.per_rank):
+                assert o.status == 0 and (o.p_last, o.q_last, o.p_second_last) == (one.p_last, one.q_last, one.p_second_last)
+                lo, hi = r.slices[rank]
+                assert torch.equal(r.all_P[rank].cpu(), one.P[lo:hi].cpu()) and torch.equal(r.all_Q[rank].cpu(), one.Q[lo:hi].cpu())
