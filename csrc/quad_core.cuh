@@ -181,6 +181,11 @@ struct TileAcc<double> {
     BQ_HD void add_one(int j, double v) { a[j] += v; }
     // Fused accumulation of the sample S*cj + C*sj (integrands with kFusedSum): two chained FMAs.
     BQ_HD void add_rot(int j, double S, double C, double cj, double sj) { a[j] = fma(C, sj, fma(S, cj, a[j])); }
+    // one whole row (kCols samples of this thread)
+    BQ_HD void add_rot_row(double S, double C, const double (&cj)[kCols], const double (&sj)[kCols]) {
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) add_rot(j, S, C, cj[j], sj[j]);
+    }
     BQ_HD void promote() {}
     BQ_HD double flush() const { return pairwise_cols<double>(a); }
     BQ_HD double flush_fused() { return pairwise_cols<double>(a); }
@@ -205,6 +210,31 @@ struct TileAcc<float> {
     }
     BQ_HD void add_one(int, float v) { kahan_add(sum, comp, v); }
     BQ_HD void add_rot(int j, float S, float C, float P, float Q) { a[j] = fmaf(C, Q, fmaf(S, P, a[j])); }
+    // One whole row.  On the GPU the columns go two at a time through the packed fp32 FMA
+    // (fma.rn.f32x2 -> SASS FFMA2, Blackwell): a three-register FFMA issues at half the fp32 rate,
+    // the packed form carries two per issue slot.  Each half is an IEEE fma, so the bits equal the
+    // scalar form the CPU tree uses.
+    BQ_HD void add_rot_row(float S, float C, const float (&P)[kCols], const float (&Q)[kCols]) {
+#if defined(__CUDA_ARCH__)
+        static_assert(kCols % 2 == 0, "columns are paired");
+        unsigned long long s2, c2;
+        asm("mov.b64 %0, {%1, %1};" : "=l"(s2) : "f"(S));
+        asm("mov.b64 %0, {%1, %1};" : "=l"(c2) : "f"(C));
+#pragma unroll
+        for (int j = 0; j < kCols; j += 2) {
+            unsigned long long a2, p2, q2;
+            asm("mov.b64 %0, {%1, %2};" : "=l"(a2) : "f"(a[j]), "f"(a[j + 1]));
+            asm("mov.b64 %0, {%1, %2};" : "=l"(p2) : "f"(P[j]), "f"(P[j + 1]));
+            asm("mov.b64 %0, {%1, %2};" : "=l"(q2) : "f"(Q[j]), "f"(Q[j + 1]));
+            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(a2) : "l"(s2), "l"(p2));
+            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(a2) : "l"(c2), "l"(q2));
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(a[j]), "=f"(a[j + 1]) : "l"(a2));
+        }
+#else
+#pragma unroll
+        for (int j = 0; j < kCols; ++j) add_rot(j, S, C, P[j], Q[j]);
+#endif
+    }
     BQ_HD void promote() {
 #pragma unroll
         for (int j = 0; j < kCols; ++j) d[j] += double(a[j]), a[j] = 0.f;

@@ -193,8 +193,7 @@ struct PartWorker {
             const Vec2<R> sc_next = sc_row[r + 1];
             const double x0_next = F::kNeedX ? x0_row[r + 1] : 0.0;
             if constexpr (kFused) {
-#pragma unroll
-                for (int j = 0; j < kCols; ++j) acc.add_rot(j, sc.x, sc.y, cj[j], sj[j]);
+                acc.add_rot_row(sc.x, sc.y, cj, sj);
                 if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();   // fp32 only; no-op in fp64
             } else {
                 R v[kCols];
@@ -223,8 +222,7 @@ struct PartWorker {
                 const Vec2<R> sc_next = sc_row[b * kUnroll + r + 1];
                 const double x0_next = F::kNeedX ? x0_row[b * kUnroll + r + 1] : 0.0;
                 if constexpr (kFused) {
-#pragma unroll
-                    for (int j = 0; j < kCols; ++j) acc.add_rot(j, sc.x, sc.y, cj[j], sj[j]);
+                    acc.add_rot_row(sc.x, sc.y, cj, sj);
                     if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();   // fp32 only
                 } else {
                     R v[kCols];
