@@ -260,6 +260,7 @@ def bench_integrate(args, env):
             "gpu_launches_per_rank": args.steps,
             "gpu_launches_note": "the %d timed steps of `value`; warm-up, the e2e arm and the extras launch the "
                                  "same kernels again outside it" % args.steps,
+            "roofline": roofline(args, value),
             "kernel_us_last_step": kern_ns / 1e3,
             "kernel_stamps_us_rank0_last_step": stamps,
             "wall_s_timed_region": wall1 - wall0,
@@ -270,6 +271,19 @@ def bench_integrate(args, env):
         }
         emit(out)
     return 0
+
+
+def roofline(args, value):
+    """Fraction of the CUDA-core issue roofline for the headline's evaluation mode (ROTATE: two fused
+    FMAs per interval).  The denominator is builder-measured (tools/peak_fp64.cu ->
+    profiles/peak_fp64_fp32.jsonl): MEASURED_PEAKS.json carries no fp64 / fp32 CUDA-core entry."""
+    if args.integrand not in ("sin", "acc", "vel") or args.eval == "direct":
+        return None
+    peak = 18563.0 if args.dtype == "fp64" else 35381.0          # G FMA instruction-lanes/s per GPU
+    bound = peak / 2.0 * args.gpus
+    return {"instr_per_interval": 2, "peak_g_fma_lanes_per_s_per_gpu": peak, "bound_g_intervals_per_s": bound,
+            "frac_of_builder_measured_peak": value / bound,
+            "note": "the bare two-FMA stream reaches 85 % of this peak in isolation (tools/dfma_bench.cu)"}
 
 
 def measure_extras(args, env):

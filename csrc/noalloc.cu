@@ -168,7 +168,9 @@ int bq_cumulative_noalloc(int device, const bq_scan_job* job, double* dP, double
     ScanPlan plan;
     rc = make_scan_plan(*job, /*rank=*/0, /*world=*/1, s->table_len, &plan);
     if (rc != BQ_OK) return rc;
-    plan.flags = 0;   // world of 1: nothing to replicate; samples are not stored by this entry point
+    // world of 1: nothing to replicate; samples are not stored by this entry point.  The evaluation
+    // flag stays: it selects the same sin/cos as bq_cumulative, so the tables are equal bit for bit.
+    plan.flags &= kScanFastTrig;
     if (plan.n_tiles > kNoAllocMaxTiles) {
         set_error("bq_cumulative_noalloc: n=%llu needs %llu tiles, the static scratch holds %llu",
                   (unsigned long long)plan.n, (unsigned long long)plan.n_tiles,

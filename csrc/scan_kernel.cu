@@ -42,6 +42,12 @@
 #include "scan_core.cuh"
 #include "scan_launch.h"
 
+#ifndef BQ_SCAN_EXTRA_AHEAD
+#define BQ_SCAN_EXTRA_AHEAD 1   // grid rounds the A parts run ahead beyond the 1024 tiles a B part may depend on
+#endif
+#ifndef BQ_SCAN_POLL_NS
+#define BQ_SCAN_POLL_NS 100
+#endif
 #ifndef BQ_SCAN_MIN_CTAS
 #define BQ_SCAN_MIN_CTAS 2      // resident CTAs per SM the register budget is set for (2 -> 128 registers)
 #endif
@@ -50,8 +56,14 @@ namespace bq {
 
 namespace {
 
-constexpr int kWarps = kScanThreads / 32;
-constexpr size_t kScanStageBytes = size_t(kWarps) * 2 * 32 * kScanItems * sizeof(double);   // 32 KB
+constexpr int kPasses = kScanThreads / 32;          // passes of a tile: part of the arithmetic tree (scan_plan.h)
+// Threads of a CTA of the launch — independent of the tile tree (a warp owns a tile whatever CTA it sits in).
+#ifndef BQ_SCAN_CTA_THREADS
+#define BQ_SCAN_CTA_THREADS 256
+#endif
+constexpr int kCtaThreads = BQ_SCAN_CTA_THREADS;
+constexpr int kWarps = kCtaThreads / 32;
+constexpr size_t kScanStageBytes = size_t(kWarps) * 2 * 32 * kScanItems * sizeof(double);   // 32 KB at 8 warps
 
 struct ScanSmem {
     uint64_t gen;
@@ -122,7 +134,7 @@ struct Waiter {
         : abort_word(aw), abort_word_w(aw), gen(g), limit_ns(limit), t0(0), spins(0), failed(false) {}
     __device__ __forceinline__ bool done(bool ok) {
         if (__all_sync(0xffffffffu, ok)) return true;
-        __nanosleep(100);      // a failed poll yields its issue slots to the warps that have work
+        __nanosleep(BQ_SCAN_POLL_NS);      // a failed poll yields its issue slots to the warps that have work
         if ((++spins & 31u) == 0u) {
             if (!t0) t0 = ptx::globaltimer();
             const bool late = ptx::globaltimer() - t0 > limit_ns;
@@ -169,7 +181,7 @@ __device__ __forceinline__ TilePos tile_pos(const ScanPlan& P, uint64_t tile) {
 // REPL = the fused all-gather (replicate) is compiled in; a separate instantiation so the
 // single-GPU / slice-only kernel carries none of its registers or staging.
 template <class F, bool REPL>
-__global__ void __launch_bounds__(kScanThreads, BQ_SCAN_MIN_CTAS) scan_kernel(const __grid_constant__ ScanParams prm) {
+__global__ void __launch_bounds__(kCtaThreads, BQ_SCAN_MIN_CTAS) scan_kernel(const __grid_constant__ ScanParams prm) {
     const ScanPlan& P = prm.P;
     const ScanState& st = prm.st;
     __shared__ ScanSmem sm;
@@ -360,7 +372,7 @@ __global__ void __launch_bounds__(kScanThreads, BQ_SCAN_MIN_CTAS) scan_kernel(co
         }
         Run2 wpre{0.0, 0.0};   // fold of the passes before this one ("warps before mine")
 #pragma unroll 1
-        for (int j = 0; j < kWarps; ++j) {
+        for (int j = 0; j < kPasses; ++j) {
             const uint32_t k0 = uint32_t(j * 32 + lane) * kScanItems;
             const uint64_t idx0 = tile * uint64_t(kScanTile) + k0;
             double v[kScanItems];
@@ -486,7 +498,7 @@ __global__ void __launch_bounds__(kScanThreads, BQ_SCAN_MIN_CTAS) scan_kernel(co
         const uint64_t first = P.tile_lo + gwarp;
         // (+1: a whole round of slack, so that what a B part reads was written an iteration ago and
         // not by the A parts running next to it — measured: 17 % of the stall samples sat in those waits)
-        uint64_t ahead = (uint64_t(kScanGroup) * kScanSuper + nwarps - 1) / nwarps + 1;
+        uint64_t ahead = (uint64_t(kScanGroup) * kScanSuper + nwarps - 1) / nwarps + BQ_SCAN_EXTRA_AHEAD;
         if (multi) ahead = (P.tile_hi - P.tile_lo + nwarps - 1) / nwarps + 1;
 #pragma unroll 1
         for (uint64_t it = 0;; ++it) {
@@ -566,7 +578,7 @@ template <class F, bool REPL>
 cudaError_t launch_scan_fr(const ScanPlan& P, const ScanState& st, unsigned grid, cudaStream_t stream) {
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(grid, 1, 1);
-    lc.blockDim = dim3(kScanThreads, 1, 1);
+    lc.blockDim = dim3(kCtaThreads, 1, 1);
     lc.stream = stream;
     // staging for the coalesced peer stores of the fused all-gather
     lc.dynamicSmemBytes = REPL ? kScanStageBytes : 0;
@@ -606,8 +618,8 @@ template <class F>
 int occupancy_f() {
     int plain = 0, repl = 0;
     cudaFuncSetAttribute(scan_kernel<F, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kScanStageBytes));
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&plain, scan_kernel<F, false>, kScanThreads, 0) != cudaSuccess ||
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&repl, scan_kernel<F, true>, kScanThreads, kScanStageBytes) !=
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&plain, scan_kernel<F, false>, kCtaThreads, 0) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&repl, scan_kernel<F, true>, kCtaThreads, kScanStageBytes) !=
             cudaSuccess) {
         cudaGetLastError();
         return 1;

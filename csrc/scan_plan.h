@@ -35,7 +35,10 @@ constexpr int kScanItems = 8;
 constexpr int kScanTile = kScanThreads * kScanItems;   // 2048 samples
 constexpr uint64_t kScanMaxN = 1ull << 34;
 constexpr int kScanGroup = 32;                          // tiles per group (one warp lane each)
-constexpr int kScanSuper = 32;                          // groups per supergroup
+#ifndef BQ_SCAN_SUPER
+#define BQ_SCAN_SUPER 32
+#endif
+constexpr int kScanSuper = BQ_SCAN_SUPER;               // groups per supergroup (<= 32: one warp lane each)
 
 enum ScanFlags : uint32_t {
     kScanReplicate = 1u,
