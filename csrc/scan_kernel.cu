@@ -48,6 +48,9 @@
 #ifndef BQ_SCAN_POLL_NS
 #define BQ_SCAN_POLL_NS 100
 #endif
+#ifndef BQ_SCAN_B_PASSES
+#define BQ_SCAN_B_PASSES 1      // passes of a tile whose lane scans the B part issues interleaved (1, 2 or 4); 2 spills at 128 registers and is 12 % slower
+#endif
 #ifndef BQ_SCAN_MIN_CTAS
 #define BQ_SCAN_MIN_CTAS 2      // resident CTAs per SM the register budget is set for (2 -> 128 registers)
 #endif
@@ -62,6 +65,8 @@ constexpr int kPasses = kScanThreads / 32;          // passes of a tile: part of
 #define BQ_SCAN_CTA_THREADS 256
 #endif
 constexpr int kCtaThreads = BQ_SCAN_CTA_THREADS;
+constexpr int kBPasses = BQ_SCAN_B_PASSES;
+static_assert(kBPasses == 1 || kBPasses == 2 || kBPasses == 4, "BQ_SCAN_B_PASSES divides the 8 passes of a tile");
 constexpr int kWarps = kCtaThreads / 32;
 constexpr size_t kScanStageBytes = size_t(kWarps) * 2 * 32 * kScanItems * sizeof(double);   // 32 KB at 8 warps
 
@@ -370,31 +375,19 @@ __global__ void __launch_bounds__(kCtaThreads, BQ_SCAN_MIN_CTAS) scan_kernel(con
             const Run pre = run_combine(head, aexcl);
             tile_excl = scan_tile_exclusive(base, pre);
         }
-        Run2 wpre{0.0, 0.0};   // fold of the passes before this one ("warps before mine")
-#pragma unroll 1
-        for (int j = 0; j < kPasses; ++j) {
+        // One pass: the values of this lane's run and the run's local totals ...
+        auto pass_values = [&](int j, double (&v)[kScanItems]) -> Run2 {
+            const uint32_t k0 = uint32_t(j * 32 + lane) * kScanItems;
+            scan_thread_values(f, P, tile * uint64_t(kScanTile) + k0, k0, m, v);
+            double p = 0.0, q = 0.0;
+#pragma unroll
+            for (int i = 0; i < kScanItems; ++i) p += v[i], q += p;
+            return Run2{p, q};
+        };
+        // ... and, once the run's exclusive prefix `full` is known, its 8 table entries.
+        auto emit = [&](int j, const double (&v)[kScanItems], const Run2& full) {
             const uint32_t k0 = uint32_t(j * 32 + lane) * kScanItems;
             const uint64_t idx0 = tile * uint64_t(kScanTile) + k0;
-            double v[kScanItems];
-            scan_thread_values(f, P, idx0, k0, m, v);
-            Run2 inc;
-            {
-                double p = 0.0, q = 0.0;
-#pragma unroll
-                for (int i = 0; i < kScanItems; ++i) p += v[i], q += p;
-                inc = Run2{p, q};
-            }
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                Run2 up{__shfl_up_sync(0xffffffffu, inc.p, d), __shfl_up_sync(0xffffffffu, inc.q, d)};
-                if (lane >= d) inc = run2_combine(up, inc, double(kScanItems * d));
-            }
-            const Run2 tot{__shfl_sync(0xffffffffu, inc.p, 31), __shfl_sync(0xffffffffu, inc.q, 31)};
-            Run2 excl{__shfl_up_sync(0xffffffffu, inc.p, 1), __shfl_up_sync(0xffffffffu, inc.q, 1)};
-            if (lane == 0) excl = Run2{0.0, 0.0};
-            const Run2 et = run2_combine(wpre, excl, double(kScanItems * lane));
-            const Run2 full = run2_combine(tile_excl, et, double(k0));
-            wpre = run2_combine(wpre, tot, double(32 * kScanItems));
             // Warp-uniform: the whole pass (256 samples) lies inside the grid and holds
             // neither P[n-1] nor P[n-2] (those go to the scalar block, slow path below).
             const uint64_t pass0 = tile * uint64_t(kScanTile) + uint64_t(j) * (32 * kScanItems);
@@ -483,6 +476,41 @@ __global__ void __launch_bounds__(kCtaThreads, BQ_SCAN_MIN_CTAS) scan_kernel(con
                         }
                     }
                 }
+            }
+        };
+        Run2 wpre{0.0, 0.0};   // fold of the passes before this one ("warps before mine")
+        // Two passes at a time: their lane scans (five dependent shuffle steps each) are independent
+        // and are issued interleaved; the arithmetic is that of the pass-by-pass walk.
+#pragma unroll 1
+        for (int j = 0; j < kPasses; j += kBPasses) {
+            double v[kBPasses][kScanItems];
+            Run2 inc[kBPasses];
+#pragma unroll
+            for (int u = 0; u < kBPasses; ++u) inc[u] = pass_values(j + u, v[u]);
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                Run2 up[kBPasses];
+#pragma unroll
+                for (int u = 0; u < kBPasses; ++u)
+                    up[u] = Run2{__shfl_up_sync(0xffffffffu, inc[u].p, d), __shfl_up_sync(0xffffffffu, inc[u].q, d)};
+#pragma unroll
+                for (int u = 0; u < kBPasses; ++u)
+                    if (lane >= d) inc[u] = run2_combine(up[u], inc[u], double(kScanItems * d));
+            }
+            Run2 tot[kBPasses], excl[kBPasses];
+#pragma unroll
+            for (int u = 0; u < kBPasses; ++u) {
+                tot[u] = Run2{__shfl_sync(0xffffffffu, inc[u].p, 31), __shfl_sync(0xffffffffu, inc[u].q, 31)};
+                excl[u] = Run2{__shfl_up_sync(0xffffffffu, inc[u].p, 1), __shfl_up_sync(0xffffffffu, inc[u].q, 1)};
+                if (lane == 0) excl[u] = Run2{0.0, 0.0};
+            }
+#pragma unroll
+            for (int u = 0; u < kBPasses; ++u) {
+                const uint32_t k0 = uint32_t((j + u) * 32 + lane) * kScanItems;
+                const Run2 et = run2_combine(wpre, excl[u], double(kScanItems * lane));
+                const Run2 full = run2_combine(tile_excl, et, double(k0));
+                wpre = run2_combine(wpre, tot[u], double(32 * kScanItems));
+                emit(j + u, v[u], full);
             }
         }
     };
