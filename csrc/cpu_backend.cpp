@@ -28,6 +28,16 @@ static dd butterfly(dd* v, int lanes) {
     return v[0];
 }
 
+// The xor butterfly over plain doubles (the kernel's warp sum of the diffusion residues).
+static double butterfly_sum(double* v, int lanes) {
+    double tmp[32];
+    for (int off = lanes / 2; off >= 1; off >>= 1) {
+        for (int l = 0; l < lanes; ++l) tmp[l] = v[l] + v[l ^ off];
+        for (int l = 0; l < lanes; ++l) v[l] = tmp[l];
+    }
+    return v[0];
+}
+
 // warp_reduce_lazy(): same shape, un-normalised pairs.
 static dd butterfly_lazy(dd* v, int lanes) {
     dd tmp[32];
@@ -45,7 +55,7 @@ struct CpuWorker {
     bool rotate;
     // column constants per virtual thread, row rotations per virtual lane
     std::vector<R> cj, sj;
-    std::vector<double> dx;
+    std::vector<double> dx, plo, qlo;
     SinCos rowrot[32];
 
     static SinCos host_sc(double ang) {
@@ -59,6 +69,8 @@ struct CpuWorker {
         cj.resize(kThreads * kCols);
         sj.resize(kThreads * kCols);
         dx.resize(kThreads * kCols);
+        plo.assign(kThreads, 0.0);
+        qlo.assign(kThreads, 0.0);
         SinCos blk[kCols];
         for (int j = 0; j < kCols; ++j) blk[j] = host_sc(f.angle(double(j * kThreads) * P.h));
         for (int t = 0; t < kThreads; ++t) {
@@ -70,8 +82,10 @@ struct CpuWorker {
                     if (F::kFusedSum) {
                         double Pc, Qc;
                         fused_consts(f, cs, Pc, Qc);
-                        cj[idx] = R(Pc);
+                        cj[idx] = fused_hi<R>(Pc, (P.flags & kFlagFineGrid) != 0u);
                         sj[idx] = R(Qc);
+                        plo[t] += Pc - double(cj[idx]);
+                        qlo[t] += Qc - double(sj[idx]);
                     } else {
                         cj[idx] = R(cs.c);
                         sj[idx] = R(cs.s);
@@ -95,6 +109,7 @@ struct CpuWorker {
         for (int t = 0; t < kThreads; ++t) total[t] = dd{0.0, 0.0}, accs[t].clear();
         R S[kMaxRows], C[kMaxRows];
         double X0[kMaxRows];
+        RowDiffusion<R, F::kFusedSum> diff[kMaxRows];     // per row lane, carried through the part
         for (uint64_t tile = lo; tile < hi; ++tile) {
             const TileGeom g = tile_geom(P, tile);
             if (rotate) {
@@ -102,8 +117,7 @@ struct CpuWorker {
                 const SinCos tb = host_sc(f.angle(fma(double(tile * P.tile_pts) + P.off, P.h, P.a)));
                 for (uint32_t k = 0; k < kMaxRows; ++k) {
                     const SinCos rb = rotate_sc(tb, rowrot[k]);
-                    S[k] = R(rb.s);
-                    C[k] = R(rb.c);
+                    diff[k].round(rb, k < g.full_rows, S[k], C[k]);     // full rows: every column uses them
                     X0[k] = fma(row_base_index(P, g, k), P.h, P.a);
                 }
             }
@@ -114,13 +128,14 @@ struct CpuWorker {
                 TileAcc<R>& acc = accs[t];
                 double rb = row_base_index(P, g, 0);
                 constexpr bool fused = F::kFusedSum;
+                const bool fine = (P.flags & kFlagFineGrid) != 0u;
                 const int fast = !(F::kTrig && (P.flags & kFlagFastTrig)) ? 0 : ((P.flags & kFlagRowK) ? 2 : 1);
                 double dcol[kCols];
                 for (int j = 0; j < kCols; ++j) dcol[j] = dxt[j];
                 for (uint32_t r = 0; r < g.full_rows; ++r) {
                     if (rotate && fused) {
                         for (int j = 0; j < kCols; ++j) acc.add_rot(j, S[r], C[r], cjt[j], sjt[j]);
-                        if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();
+                        if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote(fine);
                     } else {
                         R v[kCols];
                         if (rotate) {
@@ -151,10 +166,20 @@ struct CpuWorker {
                         }
                 }
                 if (((tile - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || tile + 1 == hi) {
-                    total[t] = dd_acc_lazy(total[t], (rotate && fused) ? acc.flush_fused() : acc.flush());
+                    total[t] = dd_acc_lazy(total[t], (rotate && fused) ? acc.flush_fused(fine) : acc.flush());
                     acc.clear();
                 }
             }
+        }
+        if (rotate && RowDiffusion<R, F::kFusedSum>::kOn) {
+            // what the row values still owe the sums (RowDiffusion): one fp64 term per thread
+            double es[kMaxRows], ec[kMaxRows], ss[kMaxRows], sc[kMaxRows];
+            for (int k = 0; k < kMaxRows; ++k) es[k] = diff[k].es, ec[k] = diff[k].ec, ss[k] = diff[k].ss, sc[k] = diff[k].sc;
+            const double ES = butterfly_sum(es, kMaxRows), EC = butterfly_sum(ec, kMaxRows);
+            const double SS = butterfly_sum(ss, kMaxRows), CC = butterfly_sum(sc, kMaxRows);
+            for (int t = 0; t < kThreads; ++t)
+                total[t] = dd_acc_lazy(total[t], diffusion_owed<R>(ES, EC, SS, CC, &cj[t * kCols], &sj[t * kCols],
+                                                                   plo[t], qlo[t]));
         }
         // block_reduce_dd(): 8 warp butterflies, then an 8-lane butterfly, one renormalisation.
         dd wsum[8];

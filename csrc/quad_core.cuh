@@ -186,9 +186,9 @@ struct TileAcc<double> {
 #pragma unroll
         for (int j = 0; j < kCols; ++j) add_rot(j, S, C, cj[j], sj[j]);
     }
-    BQ_HD void promote() {}
+    BQ_HD void promote(bool) {}
     BQ_HD double flush() const { return pairwise_cols<double>(a); }
-    BQ_HD double flush_fused() { return pairwise_cols<double>(a); }
+    BQ_HD double flush_fused(bool) { return pairwise_cols<double>(a); }
 };
 
 template <>
@@ -196,23 +196,27 @@ struct TileAcc<float> {
     // sample-by-sample integrands: Kahan in fp32 over the pairwise row sums
     float sum, comp;
     // fused integrands: fp32 FMA runs of at most kPromoteRows rows per column, promoted to fp64
-    // (the fp64 adds ride on the otherwise idle fp64 pipe; error of a run <= ~16 ulp_fp32(|run|),
-    // random in sign, so it averages out over the millions of runs of a large n)
-    float a[kCols];
+    // (the fp64 adds ride on the otherwise idle fp64 pipe).  The two products of a sample go into
+    // two accumulators per column: for a fine grid the C*Q terms (Q = sin(column * h)) are below half
+    // an ulp of the running S*P sum and a single accumulator drops them one by one — a bias, not a
+    // random rounding; kept apart they add up among themselves and meet the other sum once per run.
+    float a[kCols], c[kCols];
     double d[kCols];
     BQ_HD void clear() {
         sum = 0.f, comp = 0.f;
 #pragma unroll
-        for (int j = 0; j < kCols; ++j) a[j] = 0.f, d[j] = 0.0;
+        for (int j = 0; j < kCols; ++j) a[j] = 0.f, c[j] = 0.f, d[j] = 0.0;
     }
     BQ_HD void add_row(const float (&v)[kCols]) {
         kahan_add(sum, comp, pairwise_cols<float>(v));
     }
     BQ_HD void add_one(int, float v) { kahan_add(sum, comp, v); }
-    BQ_HD void add_rot(int j, float S, float C, float P, float Q) { a[j] = fmaf(C, Q, fmaf(S, P, a[j])); }
+    BQ_HD void add_rot(int j, float S, float C, float P, float Q) {
+        a[j] = fmaf(S, P, a[j]);
+        c[j] = fmaf(C, Q, c[j]);
+    }
     // One whole row.  On the GPU the columns go two at a time through the packed fp32 FMA
-    // (fma.rn.f32x2 -> SASS FFMA2, Blackwell): a three-register FFMA issues at half the fp32 rate,
-    // the packed form carries two per issue slot.  Each half is an IEEE fma, so the bits equal the
+    // (fma.rn.f32x2 -> SASS FFMA2, Blackwell).  Each half is an IEEE fma, so the bits equal the
     // scalar form the CPU tree uses.
     BQ_HD void add_rot_row(float S, float C, const float (&P)[kCols], const float (&Q)[kCols]) {
 #if defined(__CUDA_ARCH__)
@@ -222,32 +226,112 @@ struct TileAcc<float> {
         asm("mov.b64 %0, {%1, %1};" : "=l"(c2) : "f"(C));
 #pragma unroll
         for (int j = 0; j < kCols; j += 2) {
-            unsigned long long a2, p2, q2;
+            unsigned long long a2, b2, p2, q2;
             asm("mov.b64 %0, {%1, %2};" : "=l"(a2) : "f"(a[j]), "f"(a[j + 1]));
+            asm("mov.b64 %0, {%1, %2};" : "=l"(b2) : "f"(c[j]), "f"(c[j + 1]));
             asm("mov.b64 %0, {%1, %2};" : "=l"(p2) : "f"(P[j]), "f"(P[j + 1]));
             asm("mov.b64 %0, {%1, %2};" : "=l"(q2) : "f"(Q[j]), "f"(Q[j + 1]));
             asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(a2) : "l"(s2), "l"(p2));
-            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(a2) : "l"(c2), "l"(q2));
+            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(b2) : "l"(c2), "l"(q2));
             asm("mov.b64 {%0, %1}, %2;" : "=f"(a[j]), "=f"(a[j + 1]) : "l"(a2));
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(c[j]), "=f"(c[j + 1]) : "l"(b2));
         }
 #else
 #pragma unroll
         for (int j = 0; j < kCols; ++j) add_rot(j, S, C, P[j], Q[j]);
 #endif
     }
-    BQ_HD void promote() {
+    // End of a run of kPromoteRows rows: the S*P sum of a column joins the column's fp64 sum.  The C*Q
+    // sum follows it at the end of the flush group on a fine grid (kFlagFineGrid: it stays tiny, and
+    // an fp32 add of the two would round it to the ulp of the large one — a bias of 3e-10 on [0, pi/2]
+    // at 2^30); on a coarse grid the two are of one size and meet in an fp32 add at every run.
+    // (A packed add.f32x2 for that add measured slower than eight scalar adds.)
+    BQ_HD void promote(bool fine) {
+        if (fine) {
 #pragma unroll
-        for (int j = 0; j < kCols; ++j) d[j] += double(a[j]), a[j] = 0.f;
+            for (int j = 0; j < kCols; ++j) d[j] += double(a[j]), a[j] = 0.f;
+        } else {
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) d[j] += double(a[j] + c[j]), a[j] = 0.f, c[j] = 0.f;
+        }
     }
     BQ_HD double flush() const { return double(sum) - double(comp); }
-    BQ_HD double flush_fused() {
-        promote();
+    BQ_HD double flush_fused(bool fine) {
+        promote(fine);
+        if (fine) {
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) d[j] += double(c[j]), c[j] = 0.f;
+        }
         return pairwise_cols<double>(d);
     }
 };
 
+// Row values of the fused fp32 path, rounded with error diffusion.
+//
+// A column's fp32 accumulator adds 16 or 32 row values S_r (24 significant bits, |S_r| <= 1) one after
+// the other; past |sum| = 2 every add rounds.  On a fine grid all 2048 columns of a row carry the
+// same S_r * P_j with P_j = cos(column * h) = 1.0f, so those roundings are the same in every column
+// and change slowly from run to run: they do not average out (measured: 1.9e-10 at n = 2^32 with
+// 16-row runs against 2.8e-11 with a promotion after every row, 3.8e-13 with the diffusion).  So the row values are put on a
+// grid of 2^-18 instead — S~ = rint((S + e) * 2^18) / 2^18, e = what the earlier rows of this lane's
+// row stream still owe — which makes every partial sum of a run (< 64) exact in fp32 whenever
+// P_j = 1.0f, and never worse than before otherwise.  The grid error does not accumulate: each
+// lane carries its e from tile to tile, and what is owed at the end of a part is added to the sums
+// once, in fp64 (diffusion_owed).  Full rows only (every column uses them): all but the grid's ragged last row.
+template <class R, bool FUSED>
+struct RowDiffusion {
+    static constexpr bool kOn = false;
+    double es = 0.0, ec = 0.0, ss = 0.0, sc = 0.0;
+    BQ_HD void round(const SinCos& rb, bool, R& S, R& C) { S = R(rb.s), C = R(rb.c); }
+};
+template <>
+struct RowDiffusion<float, true> {
+    static constexpr bool kOn = true;
+    double es = 0.0, ec = 0.0;     // what this lane's row stream owes the sums
+    double ss = 0.0, sc = 0.0;     // the stream's own sums over whole tiles (for the column constants' fp32 rounding)
+    static BQ_HD float grid(double t, double& owed) {
+        constexpr double kMagic = 0x1.8p+34;            // ulp = 2^-18: (t + magic) - magic = t rounded to the grid
+        const float v = float((t + kMagic) - kMagic);
+        owed = t - double(v);
+        return v;
+    }
+    BQ_HD void round(const SinCos& rb, bool whole_tile, float& S, float& C) {
+        if (whole_tile) {
+            S = grid(rb.s + es, es);
+            C = grid(rb.c + ec, ec);
+            ss += rb.s, sc += rb.c;
+        } else {
+            S = float(rb.s), C = float(rb.c);
+        }
+    }
+};
+// The fp32 column constant that multiplies the S stream.  On a fine grid P = cos(column * h * w) sits
+// within 5e-7 of 1: it is taken as exactly 1.0f there (products with the gridded row values are then
+// exact) and the whole difference goes into the fp64 closing term below, instead of the nearest fp32
+// value 1 - k * 2^-24 whose products round, in one direction, in every row.
+template <class R>
+BQ_HD R fused_hi(double Pc, bool fine) {
+    if (sizeof(R) == 4 && fine && fabs(Pc - 1.0) <= 0x1p-20) return R(1);
+    return R(Pc);
+}
+
+// The part's closing term of one thread, in fp64:
+//   (owed S parts) * (sum of its P_j) + (owed C parts) * (sum of its Q_j)         the grid residues
+// + (sum of S) * (sum of P_j - float(P_j)) + (sum of C) * (sum of Q_j - float(Q_j))   the fp32 rounding of the
+// column constants, which is the same in every row and so a bias (7.5e-9 at n = 2^24 without this term).
+// ES, EC, SS, CC: sums over the 32 row streams; plo, qlo: the thread's own sums over its columns.
+template <class R>
+BQ_HD double diffusion_owed(double ES, double EC, double SS, double CC, const R* Pj, const R* Qj, double plo,
+                            double qlo) {
+    double ps[kCols], qs[kCols];
+#pragma unroll
+    for (int j = 0; j < kCols; ++j) ps[j] = double(Pj[j]), qs[j] = double(Qj[j]);
+    const double grid = fma(ES, pairwise_cols<double>(ps), EC * pairwise_cols<double>(qs));
+    return grid + fma(SS, plo, CC * qlo);
+}
+
 #ifndef BQ_PROMOTE_ROWS
-#define BQ_PROMOTE_ROWS 16
+#define BQ_PROMOTE_ROWS 32
 #endif
 constexpr int kPromoteRows = BQ_PROMOTE_ROWS;   // fused fp32: rows summed in fp32 before the promotion to fp64
 

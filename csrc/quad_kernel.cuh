@@ -38,7 +38,7 @@
 #define BQ_ROT_UNROLL 16
 #endif
 #ifndef BQ_ROT_UNROLL_F32
-#define BQ_ROT_UNROLL_F32 16    // = kPromoteRows: the promotion lands at the end of an unrolled body
+#define BQ_ROT_UNROLL_F32 32    // = kPromoteRows: the promotion lands at the end of an unrolled body
 #endif
 #ifndef BQ_DIRECT_UNROLL
 #define BQ_DIRECT_UNROLL 2      // rows of the DIRECT loop unrolled together (8 independent samples each)
@@ -96,12 +96,15 @@ struct PartWorker {
     const uint64_t last_tile, tile_pts;
     // column constants
     R cj[kCols], sj[kCols];
+    double plo, qlo;      // fused fp32: sums over this thread's columns of (constant - its fp32 rounding)
+    const bool fine;      // kFlagFineGrid
     double dx[kCols];     // ROTATE: x offset of the column; DIRECT: column index as double
     SinCos rowrot;        // ROTATE: rotation of row `lane` relative to the tile base
 
     __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R>* sc, double* x0)
         : P(P_), f(f_), wSC(sc), wX0(x0), h(P_.h), a(P_.a), rows(P_.rows),
-          last_tile(P_.n_tiles - 1), tile_pts(P_.tile_pts) {
+          last_tile(P_.n_tiles - 1), tile_pts(P_.tile_pts), plo(0.0), qlo(0.0),
+          fine((P_.flags & kFlagFineGrid) != 0u) {
         const int lane = threadIdx.x & 31;
         if (kRotate) {
             // Two sincos per thread for all kCols columns: the thread's own
@@ -118,8 +121,10 @@ struct PartWorker {
                 if constexpr (kFused) {
                     double Pc, Qc;
                     fused_consts(f, cs, Pc, Qc);
-                    cj[j] = R(Pc);
+                    cj[j] = fused_hi<R>(Pc, fine);
                     sj[j] = R(Qc);
+                    plo += Pc - double(cj[j]);
+                    qlo += Qc - double(sj[j]);
                 } else {
                     cj[j] = R(cs.c);
                     sj[j] = R(cs.s);
@@ -160,7 +165,7 @@ struct PartWorker {
     // this warp's private buffer.  `grp` carries the accurate tile bases of the
     // current run of 32 tiles (refreshed here when t0 starts a new run).
     __device__ __forceinline__ void group_row_bases(uint32_t t0, uint32_t nt, uint32_t lo, uint32_t hi,
-                                                    SinCos& grp, int buf) const {
+                                                    SinCos& grp, int buf, RowDiffusion<R, kFused>& diff) const {
         const int lane = threadIdx.x & 31;
         if (((t0 - lo) & 31u) == 0u) grp = group_bases(t0, hi);
         Vec2<R>* sc = wSC + buf * kBufStride + lane;
@@ -171,7 +176,13 @@ struct PartWorker {
                 const int src = int((t0 + k - lo) & 31u);
                 const SinCos tb{__shfl_sync(0xffffffffu, grp.s, src), __shfl_sync(0xffffffffu, grp.c, src)};
                 const SinCos rb = rotate_sc(tb, rowrot);
-                sc[k * kMaxRows] = Vec2<R>{R(rb.s), R(rb.c)};
+                // fused fp32: the row values of whole tiles go on a grid, this lane's row stream carrying
+                // what it owes from tile to tile (quad_core.cuh: RowDiffusion); a plain rounding otherwise
+                R rs, rc;
+                uint32_t full = rows;      // full rows of the tile: all of them, but for the grid's last tile
+                if (RowDiffusion<R, kFused>::kOn && uint64_t(t0 + k) == last_tile) full = tile_geom(P, last_tile).full_rows;
+                diff.round(rb, uint32_t(lane) < full, rs, rc);
+                sc[k * kMaxRows] = Vec2<R>{rs, rc};
                 if (F::kNeedX)
                     x0[k * kMaxRows] =
                         fma(double(uint64_t(t0 + k) * tile_pts + uint64_t(lane) * kWidth) + P.off, h, a);
@@ -194,7 +205,7 @@ struct PartWorker {
             const double x0_next = F::kNeedX ? x0_row[r + 1] : 0.0;
             if constexpr (kFused) {
                 acc.add_rot_row(sc.x, sc.y, cj, sj);
-                if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();   // fp32 only; no-op in fp64
+                if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote(fine);   // fp32 only; no-op in fp64
             } else {
                 R v[kCols];
 #pragma unroll
@@ -212,7 +223,8 @@ struct PartWorker {
     __device__ __forceinline__ void rows_rotate_blocks(const Vec2<R>* sc_row, const double* x0_row, int nblk,
                                                        TileAcc<R>& acc) const {
         constexpr int kUnroll = RotUnroll<R>::value;
-        static_assert(kMaxRows % kUnroll == 0 && kUnroll % kPromoteRows == 0, "a tile is whole blocks");
+        static_assert(kMaxRows % kUnroll == 0 && (std::is_same<R, double>::value || kUnroll % kPromoteRows == 0),
+                      "a tile is whole blocks, an fp32 run ends with a block");
         Vec2<R> sc = sc_row[0];
         double x0 = F::kNeedX ? x0_row[0] : 0.0;
 #pragma unroll 1
@@ -223,7 +235,7 @@ struct PartWorker {
                 const double x0_next = F::kNeedX ? x0_row[b * kUnroll + r + 1] : 0.0;
                 if constexpr (kFused) {
                     acc.add_rot_row(sc.x, sc.y, cj, sj);
-                    if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote();   // fp32 only
+                    if ((r & (kPromoteRows - 1)) == kPromoteRows - 1) acc.promote(fine);   // fp32 only
                 } else {
                     R v[kCols];
 #pragma unroll
@@ -302,15 +314,16 @@ struct PartWorker {
             if (lo >= hi) return total;
             const uint32_t last = uint32_t(last_tile);
             SinCos grp{0.0, 1.0};
+            RowDiffusion<R, kFused> diff;
             int buf = 0;
-            group_row_bases(lo, hi - lo < uint32_t(kFlushTiles) ? hi - lo : uint32_t(kFlushTiles), lo, hi, grp, 0);
+            group_row_bases(lo, hi - lo < uint32_t(kFlushTiles) ? hi - lo : uint32_t(kFlushTiles), lo, hi, grp, 0, diff);
             __syncwarp();
             for (uint32_t t = lo; t < hi; t += kFlushTiles) {
                 const uint32_t nt = hi - t < uint32_t(kFlushTiles) ? hi - t : uint32_t(kFlushTiles);
                 if (t + kFlushTiles < hi) {
                     const uint32_t left = hi - t - kFlushTiles;
                     group_row_bases(t + kFlushTiles, left < uint32_t(kFlushTiles) ? left : uint32_t(kFlushTiles),
-                                    lo, hi, grp, buf ^ 1);
+                                    lo, hi, grp, buf ^ 1, diff);
                 }
                 const Vec2<R>* sc_row = wSC + buf * kBufStride;
                 const double* x0_row = wX0 + buf * kBufStride;
@@ -322,10 +335,22 @@ struct PartWorker {
                     for (uint32_t k = 0; k < nt; ++k)
                         tile_rotate(t + k, sc_row + k * kMaxRows, x0_row + k * kMaxRows, acc);
                 }
-                total = dd_acc_lazy(total, kFused ? acc.flush_fused() : acc.flush());
+                total = dd_acc_lazy(total, kFused ? acc.flush_fused(fine) : acc.flush());
                 acc.clear();
                 __syncwarp();
                 buf ^= 1;
+            }
+            if constexpr (RowDiffusion<R, kFused>::kOn) {
+                // what the 32 row streams still owe the sums of this part: one fp64 term per thread
+                double es = diff.es, ec = diff.ec, ss = diff.ss, sc = diff.sc;
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) {
+                    es += __shfl_xor_sync(0xffffffffu, es, off);
+                    ec += __shfl_xor_sync(0xffffffffu, ec, off);
+                    ss += __shfl_xor_sync(0xffffffffu, ss, off);
+                    sc += __shfl_xor_sync(0xffffffffu, sc, off);
+                }
+                total = dd_acc_lazy(total, diffusion_owed<R>(es, ec, ss, sc, cj, sj, plo, qlo));
             }
         } else {
             // uniform: kernel parameters

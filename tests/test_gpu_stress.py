@@ -140,8 +140,9 @@ def test_fp32_accuracy_at_2p32(ev):
     r = bq.integrate_result("sin", 0.0, math.pi, n, "left", dtype="fp32", eval=ev, backend="cuda")
     ref = oracle_sin(0.0, math.pi, n, "left")
     assert r.status == 0
-    # ROTATE: fp32 FMA runs of 16 rows promoted to fp64; DIRECT: x rounded to fp32 (ulp(pi) = 2.4e-7)
-    bound = 1e-9 if ev == "rotate" else 5e-8
+    # ROTATE: fp32 FMA runs of 32 rows over error-diffused row values, promoted to fp64 (measured 3.8e-13);
+    # DIRECT: x rounded to fp32 (ulp(pi) = 2.4e-7)
+    bound = 1e-11 if ev == "rotate" else 5e-8
     assert abs(r.value - ref) / ref <= bound, (ev, r.value)
 
 
