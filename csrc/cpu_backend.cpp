@@ -55,7 +55,8 @@ struct CpuWorker {
     bool rotate;
     // column constants per virtual thread, row rotations per virtual lane
     std::vector<R> cj, sj;
-    std::vector<double> dx, plo, qlo;
+    std::vector<double> dx;
+    double owed4[4] = {0.0, 0.0, 0.0, 0.0};   // sums over the 2048 columns: float(P), float(Q), P - float(P), Q - float(Q)
     SinCos rowrot[32];
 
     static SinCos host_sc(double ang) {
@@ -69,8 +70,7 @@ struct CpuWorker {
         cj.resize(kThreads * kCols);
         sj.resize(kThreads * kCols);
         dx.resize(kThreads * kCols);
-        plo.assign(kThreads, 0.0);
-        qlo.assign(kThreads, 0.0);
+        std::vector<double> psum(kThreads, 0.0), qsum(kThreads, 0.0), plo(kThreads, 0.0), qlo(kThreads, 0.0);
         SinCos blk[kCols];
         for (int j = 0; j < kCols; ++j) blk[j] = host_sc(f.angle(double(j * kThreads) * P.h));
         for (int t = 0; t < kThreads; ++t) {
@@ -84,8 +84,9 @@ struct CpuWorker {
                         fused_consts(f, cs, Pc, Qc);
                         cj[idx] = fused_hi<R>(Pc, (P.flags & kFlagFineGrid) != 0u);
                         sj[idx] = R(Qc);
-                        plo[t] += Pc - double(cj[idx]);
-                        qlo[t] += Qc - double(sj[idx]);
+                        const double ph = double(cj[idx]), qh = double(sj[idx]);
+                        psum[t] += ph, qsum[t] += qh;
+                        plo[t] += Pc - ph, qlo[t] += Qc - qh;
                     } else {
                         cj[idx] = R(cs.c);
                         sj[idx] = R(cs.s);
@@ -99,6 +100,10 @@ struct CpuWorker {
             }
         }
         for (int l = 0; l < 32; ++l) rowrot[l] = host_sc(f.angle(double(l) * double(kWidth) * P.h));
+        // warp butterflies, then the 8 warp sums in order (PartWorker's constructor)
+        std::vector<double>* parts4[4] = {&psum, &qsum, &plo, &qlo};
+        for (int i = 0; i < 4; ++i)
+            for (int w = 0; w < kThreads / 32; ++w) owed4[i] += butterfly_sum(parts4[i]->data() + w * 32, 32);
     }
 
     dd part(uint32_t part_idx) const {
@@ -172,14 +177,10 @@ struct CpuWorker {
             }
         }
         if (rotate && RowDiffusion<R, F::kFusedSum>::kOn) {
-            // what the row values still owe the sums (RowDiffusion): one fp64 term per thread
-            double es[kMaxRows], ec[kMaxRows], ss[kMaxRows], sc[kMaxRows];
-            for (int k = 0; k < kMaxRows; ++k) es[k] = diff[k].es, ec[k] = diff[k].ec, ss[k] = diff[k].ss, sc[k] = diff[k].sc;
-            const double ES = butterfly_sum(es, kMaxRows), EC = butterfly_sum(ec, kMaxRows);
-            const double SS = butterfly_sum(ss, kMaxRows), CC = butterfly_sum(sc, kMaxRows);
-            for (int t = 0; t < kThreads; ++t)
-                total[t] = dd_acc_lazy(total[t], diffusion_owed<R>(ES, EC, SS, CC, &cj[t * kCols], &sj[t * kCols],
-                                                                   plo[t], qlo[t]));
+            // what the row values still owe the sums (RowDiffusion)
+            for (int k = 0; k < kMaxRows; ++k)      // lane k of the first warp settles row stream k
+                total[k] = dd_acc_lazy(total[k], diffusion_owed(diff[k].es, diff[k].ec, diff[k].ss, diff[k].sc,
+                                                                owed4[0], owed4[1], owed4[2], owed4[3]));
         }
         // block_reduce_dd(): 8 warp butterflies, then an 8-lane butterfly, one renormalisation.
         dd wsum[8];

@@ -164,7 +164,7 @@ int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, in
             P->flags |= kFlagFastTrig;
             if (w * fabs(P->h) * double(kWidth) <= 1.0 / 1024.0) P->flags |= kFlagRowK;
         }
-        if (w * fabs(P->h) * double(kWidth) <= 1.0 / 1024.0) P->flags |= kFlagFineGrid;
+        if (w * fabs(P->h) * double(kWidth) <= 1.0 / 256.0) P->flags |= kFlagFineGrid;
     }
     P->timeout_ms = 2000;
     return BQ_OK;

@@ -44,7 +44,7 @@ enum PlanFlags : uint32_t {
     kFlagSkipPublish = 2u,   // fault injection: never publish (peers time out)
     kFlagFastTrig = 4u,      // DIRECT: |angle| <= kFastTrigMax over [a, b], bounded sin/cos allowed
     kFlagRowK = 8u,          // ... and a row of a thread spans < 2^-10 rad: its samples share one multiple of pi/2
-    kFlagFineGrid = 16u,     // ROTATE fp32: the 2048 columns of a row span < 2^-10 rad (TileAcc<float>: the C*Q sums stay tiny)
+    kFlagFineGrid = 16u,     // ROTATE fp32: the 2048 columns of a row span < 2^-8 rad (TileAcc<float>: the C*Q sums stay tiny)
 };
 
 struct Plan {

@@ -288,46 +288,43 @@ template <>
 struct RowDiffusion<float, true> {
     static constexpr bool kOn = true;
     double es = 0.0, ec = 0.0;     // what this lane's row stream owes the sums
-    double ss = 0.0, sc = 0.0;     // the stream's own sums over whole tiles (for the column constants' fp32 rounding)
+    double ss = 0.0, sc = 0.0;     // sums of the stream's fp32 row values (for the column constants' fp32 rounding)
     static BQ_HD float grid(double t, double& owed) {
         constexpr double kMagic = 0x1.8p+34;            // ulp = 2^-18: (t + magic) - magic = t rounded to the grid
-        const float v = float((t + kMagic) - kMagic);
-        owed = t - double(v);
-        return v;
+        const double q = (t + kMagic) - kMagic;         // |q| <= 1 + 2^-18, 20 significant bits: float(q) is exact
+        owed = t - q;
+        return float(q);
     }
-    BQ_HD void round(const SinCos& rb, bool whole_tile, float& S, float& C) {
-        if (whole_tile) {
+    // full_row: every column uses the row (all rows but the grid's ragged last one).
+    BQ_HD void round(const SinCos& rb, bool full_row, float& S, float& C) {
+        if (full_row) {
             S = grid(rb.s + es, es);
             C = grid(rb.c + ec, ec);
-            ss += rb.s, sc += rb.c;
+            ss += double(S), sc += double(C);
         } else {
             S = float(rb.s), C = float(rb.c);
         }
     }
 };
 // The fp32 column constant that multiplies the S stream.  On a fine grid P = cos(column * h * w) sits
-// within 5e-7 of 1: it is taken as exactly 1.0f there (products with the gridded row values are then
+// within 8e-6 of 1: it is taken as exactly 1.0f there (products with the gridded row values are then
 // exact) and the whole difference goes into the fp64 closing term below, instead of the nearest fp32
 // value 1 - k * 2^-24 whose products round, in one direction, in every row.
 template <class R>
 BQ_HD R fused_hi(double Pc, bool fine) {
-    if (sizeof(R) == 4 && fine && fabs(Pc - 1.0) <= 0x1p-20) return R(1);
+    if (sizeof(R) == 4 && fine && fabs(Pc - 1.0) <= 0x1p-16) return R(1);
     return R(Pc);
 }
 
-// The part's closing term of one thread, in fp64:
-//   (owed S parts) * (sum of its P_j) + (owed C parts) * (sum of its Q_j)         the grid residues
-// + (sum of S) * (sum of P_j - float(P_j)) + (sum of C) * (sum of Q_j - float(Q_j))   the fp32 rounding of the
-// column constants, which is the same in every row and so a bias (7.5e-9 at n = 2^24 without this term).
-// ES, EC, SS, CC: sums over the 32 row streams; plo, qlo: the thread's own sums over its columns.
-template <class R>
-BQ_HD double diffusion_owed(double ES, double EC, double SS, double CC, const R* Pj, const R* Qj, double plo,
-                            double qlo) {
-    double ps[kCols], qs[kCols];
-#pragma unroll
-    for (int j = 0; j < kCols; ++j) ps[j] = double(Pj[j]), qs[j] = double(Qj[j]);
-    const double grid = fma(ES, pairwise_cols<double>(ps), EC * pairwise_cols<double>(qs));
-    return grid + fma(SS, plo, CC * qlo);
+// The part's closing term of row stream r (added by lane r of the CTA's first warp), in fp64:
+//   (what the stream owes in S) * PS + (what it owes in C) * QS                   the grid residues
+// + (its sum of S) * PLO + (its sum of C) * QLO     the fp32 rounding of the column constants, which is the
+//                                                   same in every row and so a bias (7.5e-9 at n = 2^24 without)
+// PS, QS, PLO, QLO: sums over the CTA's 2048 columns of float(P_j), float(Q_j), P_j - float(P_j),
+// Q_j - float(Q_j), formed once per launch.
+BQ_HD double diffusion_owed(double es, double ec, double ss, double sc, double PS, double QS, double PLO,
+                            double QLO) {
+    return fma(es, PS, ec * QS) + fma(ss, PLO, sc * QLO);
 }
 
 #ifndef BQ_PROMOTE_ROWS

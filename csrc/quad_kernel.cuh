@@ -96,16 +96,18 @@ struct PartWorker {
     const uint64_t last_tile, tile_pts;
     // column constants
     R cj[kCols], sj[kCols];
-    double plo, qlo;      // fused fp32: sums over this thread's columns of (constant - its fp32 rounding)
+    const double* owed4;  // fused fp32: the CTA's four constants of the part's closing term, in shared memory:
+                          // sums over all its columns of float(P_j), float(Q_j), P_j - float(P_j), Q_j - float(Q_j)
     const bool fine;      // kFlagFineGrid
     double dx[kCols];     // ROTATE: x offset of the column; DIRECT: column index as double
     SinCos rowrot;        // ROTATE: rotation of row `lane` relative to the tile base
 
-    __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R>* sc, double* x0)
+    __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R>* sc, double* x0, double* owed)
         : P(P_), f(f_), wSC(sc), wX0(x0), h(P_.h), a(P_.a), rows(P_.rows),
-          last_tile(P_.n_tiles - 1), tile_pts(P_.tile_pts), plo(0.0), qlo(0.0),
+          last_tile(P_.n_tiles - 1), tile_pts(P_.tile_pts), owed4(owed),
           fine((P_.flags & kFlagFineGrid) != 0u) {
         const int lane = threadIdx.x & 31;
+        double psum = 0.0, qsum = 0.0, plo = 0.0, qlo = 0.0;
         if (kRotate) {
             // Two sincos per thread for all kCols columns: the thread's own
             // offset, and (lane & 7)'s block offset shared through shuffles.
@@ -123,8 +125,9 @@ struct PartWorker {
                     fused_consts(f, cs, Pc, Qc);
                     cj[j] = fused_hi<R>(Pc, fine);
                     sj[j] = R(Qc);
-                    plo += Pc - double(cj[j]);
-                    qlo += Qc - double(sj[j]);
+                    const double ph = double(cj[j]), qh = double(sj[j]);
+                    psum += ph, qsum += qh;
+                    plo += Pc - ph, qlo += Qc - qh;
                 } else {
                     cj[j] = R(cs.c);
                     sj[j] = R(cs.s);
@@ -132,6 +135,29 @@ struct PartWorker {
                 dx[j] = double(threadIdx.x + kThreads * j) * h;
             }
             sincos(f.angle(double(lane) * double(kWidth) * h), &rowrot.s, &rowrot.c);
+            if constexpr (RowDiffusion<R, kFused>::kOn) {
+                // the four sums over the CTA's 2048 columns, once per launch: warp butterflies, then the
+                // 8 warp sums in order (cpu_backend.cpp does the same); owed[0..3] the totals, owed[4..] scratch
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) {
+                    psum += __shfl_xor_sync(0xffffffffu, psum, off);
+                    qsum += __shfl_xor_sync(0xffffffffu, qsum, off);
+                    plo += __shfl_xor_sync(0xffffffffu, plo, off);
+                    qlo += __shfl_xor_sync(0xffffffffu, qlo, off);
+                }
+                const int warp = threadIdx.x >> 5;
+                if (lane == 0) {
+                    owed[4 + warp * 4 + 0] = psum, owed[4 + warp * 4 + 1] = qsum;
+                    owed[4 + warp * 4 + 2] = plo, owed[4 + warp * 4 + 3] = qlo;
+                }
+                __syncthreads();
+                if (threadIdx.x < 4) {
+                    double t = 0.0;
+                    for (int w = 0; w < kThreads / 32; ++w) t += owed[4 + w * 4 + threadIdx.x];
+                    owed[threadIdx.x] = t;
+                }
+                __syncthreads();
+            }
         } else {
 #pragma unroll
             for (int j = 0; j < kCols; ++j) {
@@ -341,16 +367,12 @@ struct PartWorker {
                 buf ^= 1;
             }
             if constexpr (RowDiffusion<R, kFused>::kOn) {
-                // what the 32 row streams still owe the sums of this part: one fp64 term per thread
-                double es = diff.es, ec = diff.ec, ss = diff.ss, sc = diff.sc;
-#pragma unroll
-                for (int off = 16; off >= 1; off >>= 1) {
-                    es += __shfl_xor_sync(0xffffffffu, es, off);
-                    ec += __shfl_xor_sync(0xffffffffu, ec, off);
-                    ss += __shfl_xor_sync(0xffffffffu, ss, off);
-                    sc += __shfl_xor_sync(0xffffffffu, sc, off);
-                }
-                total = dd_acc_lazy(total, diffusion_owed<R>(es, ec, ss, sc, cj, sj, plo, qlo));
+                // What the row streams still owe the sums of this part.  Every warp carries the same 32
+                // streams (they walk the same tiles), so warp 0 settles them: lane r adds its stream's
+                // term for ALL the CTA's columns — no shuffle, four FMAs per part.
+                if (threadIdx.x < 32)
+                    total = dd_acc_lazy(total, diffusion_owed(diff.es, diff.ec, diff.ss, diff.sc, owed4[0], owed4[1],
+                                                              owed4[2], owed4[3]));
             }
         } else {
             // uniform: kernel parameters
@@ -424,8 +446,9 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     }
 
     const F f = make_functor<F>(P, sTable);
+    __shared__ double sOwed[RowDiffusion<R, Worker::kFused>::kOn && Worker::kRotate ? 4 + 4 * (kThreads / 32) : 1];
     const Worker worker(P, f, sSC + warp * 2 * Worker::kBufStride,
-                        sX0 + (F::kNeedX ? warp * 2 * Worker::kBufStride : 0));
+                        sX0 + (F::kNeedX ? warp * 2 * Worker::kBufStride : 0), sOwed);
     // absolute %globaltimer stamps of this CTA (kept by thread 0; only the finishing CTA's are used)
     uint64_t ts_prologue = 0, ts_tiles = 0;
     // The call number of the cross-GPU exchange is fetched now, by the thread that may need it at

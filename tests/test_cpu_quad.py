@@ -78,6 +78,30 @@ def test_fp32_compensated(ev):
     assert abs(v - 2.0) < 5e-8 * 2.0          # fp32 evaluation, compensated accumulation
 
 
+@pytest.mark.parametrize("a,b,n,rule", [
+    (0.0, math.pi, 1 << 26, "left"),               # the headline interval: the old bias cancelled by symmetry here
+    (0.0, math.pi / 2, (1 << 26) + 5, "mid"),      # ... and not here (6.9e-8 at 2^32 before the error diffusion)
+    (1.0, 1.5, 1 << 26, "right"),
+    (0.2, 2.9, (1 << 25) + 12345, "trap"),         # ragged last tile
+    (-3.0, 2.0, 1 << 26, "mid"),
+    (0.0, math.pi / 2, 1 << 22, "mid"),            # 4 rows per tile
+])
+def test_fp32_rotate_on_a_fine_grid_is_accurate_to_fp64_level(a, b, n, rule):
+    """fp32 FMA runs over error-diffused row values (quad_core.cuh: RowDiffusion, fused_hi,
+    diffusion_owed): on a fine grid every partial sum of a run is exact in fp32 and what the
+    roundings of the row values and of the column constants leave is added once per part in fp64."""
+    r = bq.integrate_result("sin", a, b, n, rule, dtype="fp32", eval="rotate", backend="cpu")
+    ref = oracle_sin(a, b, n, rule)
+    assert abs(r.value - ref) <= 1e-12 * abs(ref)
+
+
+def test_fp32_rotate_coarse_grid_keeps_the_old_bound():
+    # 2048 columns span more than 2^-10 rad: the two products meet in an fp32 add at every run
+    for n in (1 << 16, 1 << 20):
+        r = bq.integrate_result("sin", 0.0, math.pi, n, "left", dtype="fp32", eval="rotate", backend="cpu")
+        assert abs(r.value - oracle_sin(0.0, math.pi, n, "left")) <= 5e-9 * 2.0
+
+
 def _segments(job, rank, world):
     lib, _ = _native.load()
     res = _native.Result()
