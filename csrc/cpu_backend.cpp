@@ -81,7 +81,7 @@ struct CpuWorker {
                     const SinCos cs = rotate_sc(mine, blk[j]);
                     if (F::kFusedSum) {
                         double Pc, Qc;
-                        fused_consts(f, cs, Pc, Qc);
+                        fused_consts(f, fused_norm<F, R>(f), cs, Pc, Qc);
                         cj[idx] = fused_hi<R>(Pc, (P.flags & kFlagFineGrid) != 0u);
                         sj[idx] = R(Qc);
                         const double ph = double(cj[idx]), qh = double(sj[idx]);
@@ -121,7 +121,8 @@ struct CpuWorker {
                 // every warp of the kernel derives the same row bases for itself
                 const SinCos tb = host_sc(f.angle(fma(double(tile * P.tile_pts) + P.off, P.h, P.a)));
                 for (uint32_t k = 0; k < kMaxRows; ++k) {
-                    const SinCos rb = rotate_sc(tb, rowrot[k]);
+                    SinCos rb = rotate_sc(tb, rowrot[k]);
+                    if (F::kFusedSum && fused_norm<F, R>(f).swap) rb = SinCos{rb.c, rb.s};
                     diff[k].round(rb, k < g.full_rows, S[k], C[k]);     // full rows: every column uses them
                     X0[k] = fma(row_base_index(P, g, k), P.h, P.a);
                 }
@@ -171,7 +172,7 @@ struct CpuWorker {
                         }
                 }
                 if (((tile - lo) & (kFlushTiles - 1)) == kFlushTiles - 1 || tile + 1 == hi) {
-                    total[t] = dd_acc_lazy(total[t], (rotate && fused) ? acc.flush_fused(fine) : acc.flush());
+                    total[t] = dd_acc_lazy(total[t], (rotate && fused) ? fused_norm<F, R>(f).amp * acc.flush_fused(fine) : acc.flush());
                     acc.clear();
                 }
             }
@@ -179,8 +180,9 @@ struct CpuWorker {
         if (rotate && RowDiffusion<R, F::kFusedSum>::kOn) {
             // what the row values still owe the sums (RowDiffusion)
             for (int k = 0; k < kMaxRows; ++k)      // lane k of the first warp settles row stream k
-                total[k] = dd_acc_lazy(total[k], diffusion_owed(diff[k].es, diff[k].ec, diff[k].ss, diff[k].sc,
-                                                                owed4[0], owed4[1], owed4[2], owed4[3]));
+                total[k] = dd_acc_lazy(total[k], fused_norm<F, R>(f).amp * diffusion_owed(diff[k].es, diff[k].ec, diff[k].ss,
+                                                                                        diff[k].sc, owed4[0], owed4[1],
+                                                                                        owed4[2], owed4[3]));
         }
         // block_reduce_dd(): 8 warp butterflies, then an 8-lane butterfly, one renormalisation.
         dd wsum[8];

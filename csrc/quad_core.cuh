@@ -151,6 +151,34 @@ BQ_HD void fused_consts(const F& f, SinCos col, double& P, double& Q) {
     Q = al * col.s + be * col.c;
 }
 
+// fp32 only: the fused loop runs on the integrand divided by its amplitude, so that the column constant
+// of the large stream is cos(column offset) — within 8e-6 of 1 on a fine grid, where fused_hi() makes it
+// exactly 1.0f and the products with the gridded row values exact (RowDiffusion below).
+//   beta == 0:  f / alpha = sin(row + col) = S * cos(col) + C * sin(col)      streams (S, C)
+//   alpha == 0: f / beta  = cos(row + col) = C * cos(col) + S * (-sin(col))   streams (C, S): swapped
+// and the flush multiplies by the amplitude in fp64.  A genuine two-term combination is left as it is.
+struct FusedNorm {
+    double amp;
+    bool swap;
+};
+template <class F, class R>
+BQ_HD FusedNorm fused_norm(const F& f) {
+    if (sizeof(R) == 8) return FusedNorm{1.0, false};
+    const double al = f.fuse_alpha(), be = f.fuse_beta();
+    if (be == 0.0 && al != 0.0) return FusedNorm{al, false};
+    if (al == 0.0 && be != 0.0) return FusedNorm{be, true};
+    return FusedNorm{1.0, false};
+}
+template <class F>
+BQ_HD void fused_consts(const F& f, const FusedNorm& nm, SinCos col, double& P, double& Q) {
+    if (nm.amp == 1.0 && !nm.swap) {
+        fused_consts(f, col, P, Q);
+    } else {
+        P = col.c;
+        Q = nm.swap ? -col.s : col.s;
+    }
+}
+
 // Per-thread, per-tile accumulator.
 //   fp64: kCols independent naive sums (<= kMaxRows terms each), combined
 //         pairwise and pushed into the thread's dd total at the end of a tile.

@@ -122,7 +122,7 @@ struct PartWorker {
                 const SinCos cs = rotate_sc(mine, bj);
                 if constexpr (kFused) {
                     double Pc, Qc;
-                    fused_consts(f, cs, Pc, Qc);
+                    fused_consts(f, fused_norm<F, R>(f), cs, Pc, Qc);
                     cj[j] = fused_hi<R>(Pc, fine);
                     sj[j] = R(Qc);
                     const double ph = double(cj[j]), qh = double(sj[j]);
@@ -201,10 +201,11 @@ struct PartWorker {
             if (k < nt) {
                 const int src = int((t0 + k - lo) & 31u);
                 const SinCos tb{__shfl_sync(0xffffffffu, grp.s, src), __shfl_sync(0xffffffffu, grp.c, src)};
-                const SinCos rb = rotate_sc(tb, rowrot);
+                SinCos rb = rotate_sc(tb, rowrot);
                 // fused fp32: the row values of whole tiles go on a grid, this lane's row stream carrying
                 // what it owes from tile to tile (quad_core.cuh: RowDiffusion); a plain rounding otherwise
                 R rs, rc;
+                if (kFused && fused_norm<F, R>(f).swap) rb = SinCos{rb.c, rb.s};   // fp32, cos-type integrand: streams (C, S)
                 uint32_t full = rows;      // full rows of the tile: all of them, but for the grid's last tile
                 if (RowDiffusion<R, kFused>::kOn && uint64_t(t0 + k) == last_tile) full = tile_geom(P, last_tile).full_rows;
                 diff.round(rb, uint32_t(lane) < full, rs, rc);
@@ -361,7 +362,7 @@ struct PartWorker {
                     for (uint32_t k = 0; k < nt; ++k)
                         tile_rotate(t + k, sc_row + k * kMaxRows, x0_row + k * kMaxRows, acc);
                 }
-                total = dd_acc_lazy(total, kFused ? acc.flush_fused(fine) : acc.flush());
+                total = dd_acc_lazy(total, kFused ? fused_norm<F, R>(f).amp * acc.flush_fused(fine) : acc.flush());
                 acc.clear();
                 __syncwarp();
                 buf ^= 1;
@@ -371,8 +372,8 @@ struct PartWorker {
                 // streams (they walk the same tiles), so warp 0 settles them: lane r adds its stream's
                 // term for ALL the CTA's columns — no shuffle, four FMAs per part.
                 if (threadIdx.x < 32)
-                    total = dd_acc_lazy(total, diffusion_owed(diff.es, diff.ec, diff.ss, diff.sc, owed4[0], owed4[1],
-                                                              owed4[2], owed4[3]));
+                    total = dd_acc_lazy(total, fused_norm<F, R>(f).amp * diffusion_owed(diff.es, diff.ec, diff.ss, diff.sc,
+                                                                                      owed4[0], owed4[1], owed4[2], owed4[3]));
             }
         } else {
             // uniform: kernel parameters

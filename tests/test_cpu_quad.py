@@ -95,6 +95,17 @@ def test_fp32_rotate_on_a_fine_grid_is_accurate_to_fp64_level(a, b, n, rule):
     assert abs(r.value - ref) <= 1e-12 * abs(ref)
 
 
+@pytest.mark.parametrize("name,a,b", [("vel", 0.0, 1800.0), ("acc", 5.0, 900.0), ("vel", 100.0, 700.0)])
+def test_fp32_rotate_train_models_match_fp64(name, a, b):
+    """-ascale * sin and vscale - vscale * cos run the fused fp32 loop on the integrand divided by its
+    amplitude (quad_core.cuh: fused_norm; the cos type with its two streams swapped), so the unit
+    column constant and the exact partial sums carry over."""
+    for n, rule in ((1 << 24, "mid"), ((1 << 25) + 777, "left")):
+        r = bq.integrate_result(name, a, b, n, rule, dtype="fp32", eval="rotate", backend="cpu")
+        d = bq.integrate_result(name, a, b, n, rule, dtype="fp64", eval="rotate", backend="cpu")
+        assert abs(r.value - d.value) <= 1e-11 * abs(d.value)      # the ragged last row is outside the scheme
+
+
 def test_fp32_rotate_coarse_grid_keeps_the_old_bound():
     # 2048 columns span more than 2^-10 rad: the two products meet in an fp32 add at every run
     for n in (1 << 16, 1 << 20):

@@ -154,6 +154,14 @@ def test_fp32_rotate_accuracy_at_2p32_off_the_symmetric_interval():
     assert r.status == 0 and abs(r.value - ref) / ref <= 1e-12, r.value
 
 
+@pytest.mark.parametrize("name,a,b", [("vel", 0.0, 1800.0), ("acc", 5.0, 900.0)])
+def test_fp32_rotate_train_models_match_fp64_at_2p30(name, a, b):
+    n = 1 << 30
+    r = bq.integrate_result(name, a, b, n, "mid", dtype="fp32", eval="rotate", backend="cuda")
+    d = bq.integrate_result(name, a, b, n, "mid", dtype="fp64", eval="rotate", backend="cuda")
+    assert r.status == 0 and abs(r.value - d.value) <= 1e-12 * abs(d.value), (r.value, d.value)
+
+
 @pytest.mark.parametrize("ev", ["rotate", "direct"])
 def test_fp64_accuracy_at_2p32(ev):
     n = 1 << 32
