@@ -277,6 +277,21 @@ struct ProfileF {
         for (int j = 0; j < N; ++j) v[j] = fma(sh, double(j), v0);
         return true;
     }
+    // The same run in fp32 (dtype fp32): the cell test and the position inside the cell in fp64
+    // (an fp32 x cannot tell neighbouring samples of a fine grid apart), the N lerps as one fp32 fma each.
+    template <int N>
+    BQ_HD bool eval_run(double x_first, double x_last, float (&v)[N]) const {
+        const double u0 = x_first * inv_dx, u1 = x_last * inv_dx;
+        const int i0 = cell_of(u0), i1 = cell_of(u1);
+        if (i0 != i1) return false;
+        const float t0 = float(table[i0]);
+        const float slope = float(table[i0 + 1]) - t0;
+        const float v0 = bq_fma(slope, float(u0 - double(i0)), t0);
+        const float sh = slope * float(step_du);
+#pragma unroll
+        for (int j = 0; j < N; ++j) v[j] = bq_fma(sh, float(j), v0);
+        return true;
+    }
     template <class R>
     BQ_HD R eval_fast(R x) const { return eval(x); }
     template <class R>

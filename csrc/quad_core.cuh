@@ -125,17 +125,17 @@ struct RowDirect<VelF, double, 2> : RowDirectTrig<VelF, true> {};
 template <>
 struct RowDirect<DisF, double, 2> : RowDirectTrig<DisF, true> {};
 
-// The table integrand in fp64: the row is a run of equally spaced samples, so when its two ends
+// The table integrand: the row is a run of equally spaced samples, so when its two ends
 // share a table cell (nearly always) each sample is one fma (ProfileF::eval_run).
-template <int FAST>
-struct RowDirect<ProfileF, double, FAST> {
+template <class R, int FAST>
+struct RowDirect<ProfileF, R, FAST> {
     static BQ_HD void eval(const ProfileF& f, double rowbase, const double (&col)[kCols], double h, double a,
-                           double (&v)[kCols]) {
+                           R (&v)[kCols]) {
         const double x_first = fma(rowbase + col[0], h, a);
         const double x_last = fma(rowbase + col[kCols - 1], h, a);
         if (f.template eval_run<kCols>(x_first, x_last, v)) return;
 #pragma unroll
-        for (int j = 0; j < kCols; ++j) v[j] = point_direct<ProfileF, double, 0>(f, rowbase, col[j], h, a);
+        for (int j = 0; j < kCols; ++j) v[j] = point_direct<ProfileF, R, 0>(f, rowbase, col[j], h, a);
     }
 };
 
