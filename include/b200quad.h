@@ -36,9 +36,11 @@ enum bq_integrand {
 enum bq_rule { BQ_RULE_LEFT = 0, BQ_RULE_RIGHT = 1, BQ_RULE_MID = 2, BQ_RULE_TRAP = 3 };
 
 /* Arithmetic.  F64: fp64 evaluation, dd-compensated combines.  F32C: fp32
- * evaluation; per-thread accumulation is compensated — fp32 FMA runs of 16
- * samples promoted to fp64 (trig integrands in ROTATE mode) or pairwise + Kahan
- * (everything else) — and every cross-thread combine is dd like in F64. */
+ * evaluation; per-thread accumulation is compensated — trig integrands in ROTATE
+ * mode: fp32 FMA runs of 32 rows over error-diffused row values, promoted to fp64,
+ * with one fp64 closing term per part (on a fine grid the partial sums are exact:
+ * the result agrees with F64 to ~1e-15); everything else:
+ * pairwise + Kahan — and every cross-thread combine is dd like in F64. */
 enum bq_dtype { BQ_F64 = 0, BQ_F32C = 1 };
 
 /* How f is evaluated.  DIRECT: x_i formed and f(x_i) called per point (works
