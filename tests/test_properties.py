@@ -26,6 +26,24 @@ def test_sin_any_interval_matches_closed_form(n, rule, ev, a, width):
     assert abs(r.value - ref) <= 4e-15 * scale + 1e-18, (r.value, ref)
 
 
+@settings(max_examples=40, deadline=None)
+@given(n=st.integers(min_value=1, max_value=6_000_000), rule=st.sampled_from(RULES),
+       name=st.sampled_from(["sin", "vel", "acc"]), a=st.floats(min_value=-3.0, max_value=3.0),
+       width=st.floats(min_value=1e-3, max_value=6.0))
+def test_fp32_rotate_tracks_fp64_on_any_interval(n, rule, name, a, width):
+    """The fused fp32 loop (error-diffused row values, amplitude-normalised integrand, swapped streams
+    for the cos type, ragged last row, closing term per part) against the fp64 loop over the same tree.
+    Coarse grids round every product (a few 1e-9 of the sum of |terms|); fine ones are exact."""
+    scale_t = 1.0 if name == "sin" else 300.0          # the train models take x in seconds
+    a, b = a * scale_t, (a + width) * scale_t
+    r = bq.integrate_result(name, a, b, n, rule, dtype="fp32", eval="rotate", backend="cpu")
+    d = bq.integrate_result(name, a, b, n, rule, dtype="fp64", eval="rotate", backend="cpu")
+    peak = {"sin": 1.0, "vel": 2.0 * 122000.004 / 1800.0, "acc": 1.0}[name]    # bound on |f| (acc: ~0.71)
+    assert r.status == 0 and d.status == 0
+    # a handful of samples: each carries its own fp32 rounding (6e-8); many: they average out
+    assert abs(r.value - d.value) <= (1e-7 if n < 1000 else 1e-8) * peak * (b - a), (r.value, d.value)
+
+
 @settings(max_examples=25, deadline=None)
 @given(n=st.integers(min_value=1, max_value=200_000), rule=st.sampled_from(RULES),
        name=st.sampled_from(["sin", "vel", "profile"]), world=st.sampled_from([2, 4, 8]))
