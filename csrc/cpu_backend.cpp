@@ -115,7 +115,35 @@ struct CpuWorker {
         R S[kMaxRows], C[kMaxRows];
         double X0[kMaxRows];
         RowDiffusion<R, F::kFusedSum> diff[kMaxRows];     // per row lane, carried through the part
+        constexpr bool uniform_rows = F::kFusedSum && sizeof(R) == 8;   // PartWorker::kUniformRows
+        RowConsts rowc;
+        if (rotate && uniform_rows) fill_row_consts(P, &rowc);
         for (uint64_t tile = lo; tile < hi; ++tile) {
+            if (rotate && uniform_rows && ((tile - lo) & (kFlushTiles - 1)) == 0) {
+                // PartWorker::run_uniform: a flush group of full tiles, none of them the grid's last
+                const uint64_t nt = hi - tile < uint64_t(kFlushTiles) ? hi - tile : uint64_t(kFlushTiles);
+                if (P.rows == uint32_t(kMaxRows) && tile + nt - 1 < P.n_tiles - 1) {
+                    const SinCos tb = host_sc(f.angle(fma(double(tile * P.tile_pts) + P.off, P.h, P.a)));
+                    const bool fine = (P.flags & kFlagFineGrid) != 0u;
+                    for (int t = 0; t < kThreads; ++t) {
+                        R A[kCols], B[kCols];
+                        for (int j = 0; j < kCols; ++j) {
+                            const R pj = cj[t * kCols + j], qj = sj[t * kCols + j];
+                            A[j] = R(fma(tb.s, double(pj), tb.c * double(qj)));
+                            B[j] = R(fma(tb.c, double(pj), -(tb.s * double(qj))));
+                        }
+                        TileAcc<R>& acc = accs[t];
+                        for (uint64_t k = 0; k < nt; ++k)
+                            for (int r = 0; r < kMaxRows; ++r)
+                                for (int j = 0; j < kCols; ++j)
+                                    acc.add_rot(j, R(rowc.cs[k * kMaxRows + r][0]), R(rowc.cs[k * kMaxRows + r][1]), A[j], B[j]);
+                        total[t] = dd_acc_lazy(total[t], fused_norm<F, R>(f).amp * acc.flush_fused(fine));
+                        acc.clear();
+                    }
+                    tile += nt - 1;
+                    continue;
+                }
+            }
             const TileGeom g = tile_geom(P, tile);
             if (rotate) {
                 // every warp of the kernel derives the same row bases for itself

@@ -170,6 +170,29 @@ int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, in
     return BQ_OK;
 }
 
+void fill_row_consts(const Plan& P, RowConsts* out) {
+    // angle(x) = x for sin, x / tscale for the train models (integrands.cuh)
+    const bool scaled = P.integrand != BQ_F_SIN;
+    const double tscale = scaled ? P.p[0] : 1.0;
+    struct Cache {
+        bool valid = false;
+        double h = 0.0, tscale = 0.0;
+        RowConsts rc;
+    };
+    static thread_local Cache cache;
+    if (!(cache.valid && cache.h == P.h && cache.tscale == tscale)) {
+        for (int r = 0; r < kFlushTiles * kMaxRows; ++r) {
+            const double x = double(r) * double(kWidth) * P.h;
+            double sn, cs;
+            ::sincos(scaled ? x / tscale : x, &sn, &cs);
+            cache.rc.cs[r][0] = cs;
+            cache.rc.cs[r][1] = sn;
+        }
+        cache.h = P.h, cache.tscale = tscale, cache.valid = true;
+    }
+    *out = cache.rc;
+}
+
 // Closed form of sum_{i<n} sin(a + (i+off) h) = sin(a + off h + (n-1)h/2) sin(nh/2) / sin(h/2),
 // evaluated in long double (x87 80-bit on the hosts this runs on).
 long double oracle_sin_sum(double a, double b, uint64_t n, int rule) {

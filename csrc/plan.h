@@ -75,6 +75,17 @@ constexpr double kTscale = 286.4788975;
 constexpr double kAscale = 0.2365890;
 constexpr double kVscale = 67.7777777;
 
+// ROTATE, fused fp64 loop: (cos, sin) of the angle of row r of a flush group relative to the group's
+// first tile base, angle(r * kWidth * h), r < kFlushTiles * kMaxRows.  They are launch constants, so
+// they ride in the kernel parameters (constant bank) and enter the FMAs as uniform-register operands:
+// one register read fewer per DFMA, which lifts the two-FMA stream from 86 % to 94 % of the fp64 issue
+// rate (tools/dfma_bench.cu).  The host computes them with its libm for the GPU and the CPU backend
+// alike (cached per thread for the last (integrand, h, tscale)).
+struct RowConsts {
+    double cs[kFlushTiles * kMaxRows][2];
+};
+void fill_row_consts(const Plan& P, RowConsts* out);
+
 // Fills every derived field.  Returns a bq_status.
 int make_plan(const bq_job& job, int rank, int world, uint32_t rows_override, int table_len,
               Plan* out);

@@ -86,6 +86,8 @@ template <class F, class R, int MODE>
 struct PartWorker {
     static constexpr bool kRotate = (MODE == BQ_EVAL_ROTATE);
     static constexpr bool kFused = F::kFusedSum;   // see SinF / fused_consts
+    // fused fp64: row constants as uniform operands, per-column values re-derived once per flush group
+    static constexpr bool kUniformRows = kRotate && kFused && sizeof(R) == 8;
 
     const Plan& P;        // kernel parameter (constant bank)
     const F& f;
@@ -96,15 +98,17 @@ struct PartWorker {
     const uint64_t last_tile, tile_pts;
     // column constants
     R cj[kCols], sj[kCols];
+    const RowConsts* rowc; // fused fp64: the row constants in the kernel parameters (kUniformRows), else null
     const double* owed4;  // fused fp32: the CTA's four constants of the part's closing term, in shared memory:
                           // sums over all its columns of float(P_j), float(Q_j), P_j - float(P_j), Q_j - float(Q_j)
     const bool fine;      // kFlagFineGrid
     double dx[kCols];     // ROTATE: x offset of the column; DIRECT: column index as double
     SinCos rowrot;        // ROTATE: rotation of row `lane` relative to the tile base
 
-    __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R>* sc, double* x0, double* owed)
+    __device__ __forceinline__ PartWorker(const Plan& P_, const F& f_, Vec2<R>* sc, double* x0, double* owed,
+                                          const RowConsts* rc)
         : P(P_), f(f_), wSC(sc), wX0(x0), h(P_.h), a(P_.a), rows(P_.rows),
-          last_tile(P_.n_tiles - 1), tile_pts(P_.tile_pts), owed4(owed),
+          last_tile(P_.n_tiles - 1), tile_pts(P_.tile_pts), rowc(rc), owed4(owed),
           fine((P_.flags & kFlagFineGrid) != 0u) {
         const int lane = threadIdx.x & 31;
         double psum = 0.0, qsum = 0.0, plo = 0.0, qlo = 0.0;
@@ -327,6 +331,56 @@ struct PartWorker {
         }
     }
 
+    // Fused fp64 (sin, acc, vel): the samples of a flush group of full tiles, as
+    //   f(row r, column j) = A_j * cos(rho_r) + B_j * sin(rho_r),   rho_r = angle(r * kWidth * h), r < 128,
+    //   A_j = Sb * P_j + Cb * Q_j,  B_j = Cb * P_j - Sb * Q_j       (Sb, Cb): sincos of the group's base angle
+    // i.e. the rotation is applied to the column side once per group (4 fp64 instructions per column per
+    // 128 rows) and the row side is the same 128 constants for every group of the launch.  Those sit in
+    // the kernel parameters, so the two FMAs of a sample read them as uniform-register operands
+    // (SASS: LDCU.64 UR, c[0x0][UR+imm]; DFMA R, R, UR, R) — two register reads per DFMA instead of
+    // three, no shared memory and no warp synchronisation in the loop.  The group that holds the
+    // grid's last tile, and tiles of fewer than kMaxRows rows (small n), take the general path.
+    __device__ __forceinline__ dd run_uniform(uint32_t lo, uint32_t hi) const {
+        dd total{0.0, 0.0};
+        if (lo >= hi) return total;
+        TileAcc<R> acc;
+        acc.clear();
+        const uint32_t last = uint32_t(last_tile);
+        SinCos grp{0.0, 1.0};
+        RowDiffusion<R, kFused> diff;   // (no state in fp64)
+#pragma unroll 1
+        for (uint32_t t = lo; t < hi; t += kFlushTiles) {
+            const uint32_t nt = hi - t < uint32_t(kFlushTiles) ? hi - t : uint32_t(kFlushTiles);
+            if (rows == uint32_t(kMaxRows) && t + nt - 1 < last) {
+                if (((t - lo) & 31u) == 0u) grp = group_bases(t, hi);
+                const int src = int((t - lo) & 31u);
+                const double sb = __shfl_sync(0xffffffffu, grp.s, src), cb = __shfl_sync(0xffffffffu, grp.c, src);
+                R A[kCols], B[kCols];
+#pragma unroll
+                for (int j = 0; j < kCols; ++j) {
+                    A[j] = fma(sb, cj[j], cb * sj[j]);
+                    B[j] = fma(cb, cj[j], -(sb * sj[j]));
+                }
+#pragma unroll 1
+                for (uint32_t k = 0; k < nt; ++k) {
+#pragma unroll
+                    for (int r = 0; r < kMaxRows; ++r) {
+                        const double cr = rowc->cs[k * kMaxRows + r][0], sr = rowc->cs[k * kMaxRows + r][1];
+                        acc.add_rot_row(cr, sr, A, B);      // a_j = fma(sr, B_j, fma(cr, A_j, a_j))
+                    }
+                }
+            } else {
+                group_row_bases(t, nt, lo, hi, grp, 0, diff);
+                __syncwarp();
+                for (uint32_t k = 0; k < nt; ++k) tile_rotate(t + k, wSC + k * kMaxRows, wX0 + k * kMaxRows, acc);
+                __syncwarp();
+            }
+            total = dd_acc_lazy(total, acc.flush_fused(fine));
+            acc.clear();
+        }
+        return total;
+    }
+
     // All tiles of one part; returns this thread's dd total.  In ROTATE mode a
     // warp is self-sufficient (its own bases, its own shared-memory buffer), so
     // the tile loop has no CTA-wide barrier, and a flush group of full tiles
@@ -336,7 +390,9 @@ struct PartWorker {
         dd total{0.0, 0.0};
         TileAcc<R> acc;
         acc.clear();
-        if (kRotate) {
+        if constexpr (kUniformRows) {
+            return run_uniform(uint32_t(lo64), uint32_t(hi64));
+        } else if (kRotate) {
             const uint32_t lo = uint32_t(lo64), hi = uint32_t(hi64);   // n_tiles < 2^31
             if (lo >= hi) return total;
             const uint32_t last = uint32_t(last_tile);
@@ -400,13 +456,24 @@ struct PartWorker {
 constexpr int kBatchChunks = 8;
 constexpr int kBatchSlots = kBatchChunks * kPartsPerChunk;
 
-struct QuadParams {
+template <bool ROWC>
+struct QuadParamsT {
     Plan P;            // 152 bytes, rides in the kernel parameter buffer
     DeviceState st;
+    __host__ __device__ const RowConsts* rowc() const { return nullptr; }
 };
+template <>
+struct QuadParamsT<true> {
+    Plan P;
+    DeviceState st;
+    RowConsts rc;      // 2 KB more for the fused fp64 ROTATE kernels (PartWorker::run_uniform)
+    __host__ __device__ const RowConsts* rowc() const { return &rc; }
+};
+template <class F, class R, int MODE>
+using QuadParams = QuadParamsT<PartWorker<F, R, MODE>::kUniformRows>;
 
 template <class F, class R, int MODE>
-__global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __grid_constant__ QuadParams prm) {
+__global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __grid_constant__ QuadParams<F, R, MODE> prm) {
     const Plan& P = prm.P;
     const DeviceState& st = prm.st;
     // warp-private row-base buffers (ROTATE only), sized by rotate_smem_bytes()
@@ -449,7 +516,7 @@ __global__ void __launch_bounds__(kThreads, BQ_MIN_CTAS) quad_kernel(const __gri
     const F f = make_functor<F>(P, sTable);
     __shared__ double sOwed[RowDiffusion<R, Worker::kFused>::kOn && Worker::kRotate ? 4 + 4 * (kThreads / 32) : 1];
     const Worker worker(P, f, sSC + warp * 2 * Worker::kBufStride,
-                        sX0 + (F::kNeedX ? warp * 2 * Worker::kBufStride : 0), sOwed);
+                        sX0 + (F::kNeedX ? warp * 2 * Worker::kBufStride : 0), sOwed, prm.rowc());
     // absolute %globaltimer stamps of this CTA (kept by thread 0; only the finishing CTA's are used)
     uint64_t ts_prologue = 0, ts_tiles = 0;
     // The call number of the cross-GPU exchange is fetched now, by the thread that may need it at
@@ -693,9 +760,10 @@ constexpr size_t rotate_smem_bytes() {
 
 template <class F, class R, int MODE>
 inline cudaError_t launch_one(const Plan& P, const DeviceState& st, const LaunchConfig& cfg, cudaStream_t stream) {
-    QuadParams prm;
+    QuadParams<F, R, MODE> prm;
     prm.P = P;
     prm.st = st;
+    if constexpr (PartWorker<F, R, MODE>::kUniformRows) fill_row_consts(P, &prm.rc);
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(cfg.grid, 1, 1);
     lc.blockDim = dim3(kThreads, 1, 1);
