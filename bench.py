@@ -283,7 +283,8 @@ def roofline(args, value):
     bound = peak / 2.0 * args.gpus
     return {"instr_per_interval": 2, "peak_g_fma_lanes_per_s_per_gpu": peak, "bound_g_intervals_per_s": bound,
             "frac_of_builder_measured_peak": value / bound,
-            "note": "the bare two-FMA stream reaches 85 % of this peak in isolation (tools/dfma_bench.cu)"}
+            "note": "fp64: the two-FMA stream with uniform-register row operands reaches 97 % of this peak in isolation, "
+                    "86 % with three register operands (tools/dfma_bench.cu)"}
 
 
 def measure_extras(args, env):
