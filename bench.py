@@ -252,7 +252,7 @@ def bench_integrate(args, env):
             "e2e": {"value": e2e_value, "unit": "Gintervals/s",
                     "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": bytes_h2d(), "d2h_bytes_per_step": bytes_d2h(),
-                    "h2d_path": "job description (sizeof Plan) in the kernel-launch parameter buffer; "
+                    "h2d_path": "job description (sizeof Plan) + the 128 row constants of the fp64 loop, in the kernel-launch parameter buffer; "
                                 "the workload has no input tensors",
                     "d2h_path": "result block written by the kernel into pinned mapped host memory; the host "
                                 "watches the block's completion word and reads the float from it"},

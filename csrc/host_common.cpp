@@ -229,7 +229,7 @@ int bq_register_custom_integrand(bq_custom_launch_fn launch, bq_custom_eval_fn e
 }
 const char* bq_last_error(void) { return bq::last_error(); }
 const double* bq_default_profile(int* len) { return bq::default_profile(len); }
-size_t bq_sizeof_params(void) { return sizeof(bq::Plan); }
+size_t bq_sizeof_params(void) { return sizeof(bq::Plan) + sizeof(bq::RowConsts); }
 double bq_sin_bounded(double x) { return bq::sincos_bounded<false>(x); }
 double bq_cos_bounded(double x) { return bq::sincos_bounded<true>(x); }
 double bq_oracle_sin_sum(double a, double b, uint64_t n, int rule) {

@@ -167,7 +167,8 @@ const char* bq_version(void);
 const char* bq_last_error(void);               /* thread-local message */
 int bq_cuda_device_count(void);                /* 0 when no driver / no GPU */
 const double* bq_default_profile(int* len);    /* the 1801-entry table */
-/* Bytes moved host->device per call (the parameter block). */
+/* Bytes moved host->device per call: the job description (the plan) and, for the fused fp64 ROTATE
+ * kernels, the 128 row constants — both ride in the kernel-launch parameter buffer. */
 size_t bq_sizeof_params(void);
 
 /* The bounded-argument sin / cos that DIRECT evaluation uses when the plan has verified
