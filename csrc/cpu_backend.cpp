@@ -122,7 +122,7 @@ struct CpuWorker {
             if (rotate && uniform_rows && ((tile - lo) & (kFlushTiles - 1)) == 0) {
                 // PartWorker::run_uniform: a flush group of full tiles, none of them the grid's last
                 const uint64_t nt = hi - tile < uint64_t(kFlushTiles) ? hi - tile : uint64_t(kFlushTiles);
-                if (P.rows == uint32_t(kMaxRows) && tile + nt - 1 < P.n_tiles - 1) {
+                if (tile + nt - 1 < P.n_tiles - 1) {
                     const SinCos tb = host_sc(f.angle(fma(double(tile * P.tile_pts) + P.off, P.h, P.a)));
                     const bool fine = (P.flags & kFlagFineGrid) != 0u;
                     for (int t = 0; t < kThreads; ++t) {
@@ -133,10 +133,9 @@ struct CpuWorker {
                             B[j] = R(fma(tb.c, double(pj), -(tb.s * double(qj))));
                         }
                         TileAcc<R>& acc = accs[t];
-                        for (uint64_t k = 0; k < nt; ++k)
-                            for (int r = 0; r < kMaxRows; ++r)
-                                for (int j = 0; j < kCols; ++j)
-                                    acc.add_rot(j, R(rowc.cs[k * kMaxRows + r][0]), R(rowc.cs[k * kMaxRows + r][1]), A[j], B[j]);
+                        for (uint64_t q = 0; q < nt * P.rows; ++q)      // nt * rows consecutive rows
+                            for (int j = 0; j < kCols; ++j)
+                                acc.add_rot(j, R(rowc.cs[q][0]), R(rowc.cs[q][1]), A[j], B[j]);
                         total[t] = dd_acc_lazy(total[t], fused_norm<F, R>(f).amp * acc.flush_fused(fine));
                         acc.clear();
                     }

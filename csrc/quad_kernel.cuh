@@ -339,7 +339,7 @@ struct PartWorker {
     // the kernel parameters, so the two FMAs of a sample read them as uniform-register operands
     // (SASS: LDCU.64 UR, c[0x0][UR+imm]; DFMA R, R, UR, R) — two register reads per DFMA instead of
     // three, no shared memory and no warp synchronisation in the loop.  The group that holds the
-    // grid's last tile, and tiles of fewer than kMaxRows rows (small n), take the general path.
+    // grid's last tile (which may be ragged) takes the general path.
     __device__ __forceinline__ dd run_uniform(uint32_t lo, uint32_t hi) const {
         dd total{0.0, 0.0};
         if (lo >= hi) return total;
@@ -351,7 +351,7 @@ struct PartWorker {
 #pragma unroll 1
         for (uint32_t t = lo; t < hi; t += kFlushTiles) {
             const uint32_t nt = hi - t < uint32_t(kFlushTiles) ? hi - t : uint32_t(kFlushTiles);
-            if (rows == uint32_t(kMaxRows) && t + nt - 1 < last) {
+            if (t + nt - 1 < last) {          // full tiles of `rows` rows each: nt * rows consecutive rows
                 if (((t - lo) & 31u) == 0u) grp = group_bases(t, hi);
                 const int src = int((t - lo) & 31u);
                 const double sb = __shfl_sync(0xffffffffu, grp.s, src), cb = __shfl_sync(0xffffffffu, grp.c, src);
@@ -361,13 +361,19 @@ struct PartWorker {
                     A[j] = fma(sb, cj[j], cb * sj[j]);
                     B[j] = fma(cb, cj[j], -(sb * sj[j]));
                 }
+                if (rows == uint32_t(kMaxRows)) {
 #pragma unroll 1
-                for (uint32_t k = 0; k < nt; ++k) {
+                    for (uint32_t k = 0; k < nt; ++k) {
 #pragma unroll
-                    for (int r = 0; r < kMaxRows; ++r) {
-                        const double cr = rowc->cs[k * kMaxRows + r][0], sr = rowc->cs[k * kMaxRows + r][1];
-                        acc.add_rot_row(cr, sr, A, B);      // a_j = fma(sr, B_j, fma(cr, A_j, a_j))
+                        for (int r = 0; r < kMaxRows; ++r) {
+                            const double cr = rowc->cs[k * kMaxRows + r][0], sr = rowc->cs[k * kMaxRows + r][1];
+                            acc.add_rot_row(cr, sr, A, B);      // a_j = fma(sr, B_j, fma(cr, A_j, a_j))
+                        }
                     }
+                } else {                           // tiles of fewer than kMaxRows rows (n below ~1.5e8)
+                    const uint32_t nq = nt * rows;
+#pragma unroll 4
+                    for (uint32_t q = 0; q < nq; ++q) acc.add_rot_row(rowc->cs[q][0], rowc->cs[q][1], A, B);
                 }
             } else {
                 group_row_bases(t, nt, lo, hi, grp, 0, diff);
