@@ -40,8 +40,8 @@ def test_fp32_rotate_tracks_fp64_on_any_interval(n, rule, name, a, width):
     d = bq.integrate_result(name, a, b, n, rule, dtype="fp64", eval="rotate", backend="cpu")
     peak = {"sin": 1.0, "vel": 2.0 * 122000.004 / 1800.0, "acc": 1.0}[name]    # bound on |f| (acc: ~0.71)
     assert r.status == 0 and d.status == 0
-    # a handful of samples: each carries its own fp32 rounding (6e-8); many: they average out
-    assert abs(r.value - d.value) <= (1e-7 if n < 1000 else 1e-8) * peak * (b - a), (r.value, d.value)
+    # a few rows of samples: all columns of a row share the row value's fp32 rounding (6e-8); many rows: it averages out
+    assert abs(r.value - d.value) <= (3e-7 if n < 100_000 else 1e-8) * peak * (b - a), (r.value, d.value)
 
 
 @settings(max_examples=25, deadline=None)
