@@ -48,6 +48,12 @@ static dd butterfly_lazy(dd* v, int lanes) {
     return v[0];
 }
 
+// PartWorker::tile_rotate, fused fp32: the ragged last row's share of the column constants' rounding.
+static inline void ragged_row_owed(TileAcc<float>& acc, int j, float S, float C, double plo, double qlo) {
+    acc.d[j] += fma(double(S), plo, double(C) * qlo);
+}
+static inline void ragged_row_owed(TileAcc<double>&, int, double, double, double, double) {}
+
 template <class F, class R>
 struct CpuWorker {
     const Plan& P;
@@ -55,7 +61,7 @@ struct CpuWorker {
     bool rotate;
     // column constants per virtual thread, row rotations per virtual lane
     std::vector<R> cj, sj;
-    std::vector<double> dx;
+    std::vector<double> dx, plo_col, qlo_col;   // per column: constant - its fp32 value (fused fp32, ragged last row)
     double owed4[4] = {0.0, 0.0, 0.0, 0.0};   // sums over the 2048 columns: float(P), float(Q), P - float(P), Q - float(Q)
     SinCos rowrot[32];
 
@@ -70,6 +76,8 @@ struct CpuWorker {
         cj.resize(kThreads * kCols);
         sj.resize(kThreads * kCols);
         dx.resize(kThreads * kCols);
+        plo_col.assign(kThreads * kCols, 0.0);
+        qlo_col.assign(kThreads * kCols, 0.0);
         std::vector<double> psum(kThreads, 0.0), qsum(kThreads, 0.0), plo(kThreads, 0.0), qlo(kThreads, 0.0);
         SinCos blk[kCols];
         for (int j = 0; j < kCols; ++j) blk[j] = host_sc(f.angle(double(j * kThreads) * P.h));
@@ -87,6 +95,7 @@ struct CpuWorker {
                         const double ph = double(cj[idx]), qh = double(sj[idx]);
                         psum[t] += ph, qsum[t] += qh;
                         plo[t] += Pc - ph, qlo[t] += Qc - qh;
+                        plo_col[idx] = Pc - ph, qlo_col[idx] = Qc - qh;
                     } else {
                         cj[idx] = R(cs.c);
                         sj[idx] = R(cs.s);
@@ -189,9 +198,10 @@ struct CpuWorker {
                     const uint32_t r = g.full_rows;
                     for (int j = 0; j < kCols; ++j)
                         if (uint32_t(t + kThreads * j) < g.rem) {
-                            if (rotate && fused)
+                            if (rotate && fused) {
                                 acc.add_rot(j, S[r], C[r], cjt[j], sjt[j]);
-                            else
+                                ragged_row_owed(acc, j, S[r], C[r], plo_col[t * kCols + j], qlo_col[t * kCols + j]);
+                            } else
                                 acc.add_one(j, rotate ? point_rotate<F, R>(f, S[r], C[r], cjt[j], sjt[j],
                                                                            X0[r], dxt[j])
                                                       : fast ? point_direct<F, R, 1>(f, rb, dxt[j], P.h, P.a)

@@ -295,9 +295,21 @@ struct PartWorker {
 #pragma unroll
             for (int j = 0; j < kCols; ++j)
                 if (threadIdx.x + kThreads * j < rem) {
-                    if constexpr (kFused)
+                    if constexpr (kFused) {
                         acc.add_rot(j, sc.x, sc.y, cj[j], sj[j]);
-                    else
+                        if constexpr (RowDiffusion<R, kFused>::kOn) {
+                            // The ragged last row is outside the parts' closing terms (not every column
+                            // uses it): what the fp32 rounding of its column constants leaves — on a fine
+                            // grid P_j is taken as 1.0f, up to 8e-6 off — is added here, in fp64.  Once per
+                            // launch, so the constants are simply derived again.
+                            SinCos mine, blk;
+                            sincos(f.angle(double(threadIdx.x) * h), &mine.s, &mine.c);
+                            sincos(f.angle(double(j * kThreads) * h), &blk.s, &blk.c);
+                            double Pc, Qc;
+                            fused_consts(f, fused_norm<F, R>(f), rotate_sc(mine, blk), Pc, Qc);
+                            acc.d[j] += fma(double(sc.x), Pc - double(cj[j]), double(sc.y) * (Qc - double(sj[j])));
+                        }
+                    } else
                         acc.add_one(j, point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]));
                 }
         }

@@ -23,7 +23,7 @@ def test_sin_any_interval_matches_closed_form(n, rule, ev, a, width):
     # the Riemann sum may cancel (e.g. around a zero of the integral): bound against the sum of |terms|
     scale = max(abs(ref), width * 0.05, 1e-300)
     assert r.status == 0
-    assert abs(r.value - ref) <= 4e-15 * scale + 1e-18, (r.value, ref)
+    assert abs(r.value - ref) <= 6e-15 * scale + 1e-18, (r.value, ref)
 
 
 @settings(max_examples=40, deadline=None, derandomize=True)
