@@ -82,6 +82,19 @@ __device__ __forceinline__ dd warp_reduce_lazy(dd v) {
     return v;
 }
 
+// (P_j - float P_j, Q_j - float Q_j) of column j of thread tid, derived afresh: for the ragged last row
+// of the fused fp32 path (PartWorker::tile_rotate), once per launch.  Not inlined, so that its two
+// libdevice sincos stay out of the register budget of the kernel's loops.
+template <class F, class R>
+__device__ __noinline__ double2 column_consts_lo(F f, double h, unsigned tid, int j, double cjv, double sjv) {
+    SinCos mine, blk;
+    sincos(f.angle(double(tid) * h), &mine.s, &mine.c);
+    sincos(f.angle(double(j * kThreads) * h), &blk.s, &blk.c);
+    double Pc, Qc;
+    fused_consts(f, fused_norm<F, R>(f), rotate_sc(mine, blk), Pc, Qc);
+    return make_double2(Pc - cjv, Qc - sjv);
+}
+
 template <class F, class R, int MODE>
 struct PartWorker {
     static constexpr bool kRotate = (MODE == BQ_EVAL_ROTATE);
@@ -302,12 +315,8 @@ struct PartWorker {
                             // uses it): what the fp32 rounding of its column constants leaves — on a fine
                             // grid P_j is taken as 1.0f, up to 8e-6 off — is added here, in fp64.  Once per
                             // launch, so the constants are simply derived again.
-                            SinCos mine, blk;
-                            sincos(f.angle(double(threadIdx.x) * h), &mine.s, &mine.c);
-                            sincos(f.angle(double(j * kThreads) * h), &blk.s, &blk.c);
-                            double Pc, Qc;
-                            fused_consts(f, fused_norm<F, R>(f), rotate_sc(mine, blk), Pc, Qc);
-                            acc.d[j] += fma(double(sc.x), Pc - double(cj[j]), double(sc.y) * (Qc - double(sj[j])));
+                            const double2 lo = column_consts_lo<F, R>(f, h, threadIdx.x, j, double(cj[j]), double(sj[j]));
+                            acc.d[j] += fma(double(sc.x), lo.x, double(sc.y) * lo.y);
                         }
                     } else
                         acc.add_one(j, point_rotate<F, R>(f, sc.x, sc.y, cj[j], sj[j], x0, dx[j]));
