@@ -158,6 +158,92 @@ __global__ void __launch_bounds__(256, 2) k(double* out, int rows, float h) {
     if (s == -1.2345) out[0] = s;
 }
 
+// MODE 7 (own kernel): the row constants ride in the kernel parameters and enter the packed FMAs as
+// uniform operands; the per-column pairs (A_j, A_j+1), (B_j, B_j+1) sit in registers (the fp64 loop's form).
+struct RowParamsF {
+    double* out;
+    int groups, nt;
+    float rc[128][2];
+};
+template <int PROMO>
+__global__ void __launch_bounds__(256, 2) k_uniform(const __grid_constant__ RowParamsF p) {
+    unsigned long long A2[4], B2[4], a2[4], b2[4];
+    double d[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        A2[j] = pack(1.0f + 1e-3f * threadIdx.x, 0.5f + j);
+        B2[j] = pack(1e-3f * j, 2e-3f * threadIdx.x);
+        a2[j] = pack(0.f, 0.f);
+        b2[j] = pack(0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) d[j] = 0.0;
+    for (int g = 0; g < p.groups; ++g) {
+#pragma unroll 1
+        for (int kk = 0; kk < p.nt; ++kk) {
+#pragma unroll
+            for (int r = 0; r < 32; ++r) {
+                const float c = p.rc[kk * 32 + r][0], s = p.rc[kk * 32 + r][1];
+                const unsigned long long c2 = pack(c, c), s2 = pack(s, s);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) fma2(a2[j], c2, A2[j]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) fma2(b2[j], s2, B2[j]);
+                if ((r % PROMO) == PROMO - 1) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        float lo, hi;
+                        unpack(a2[j], lo, hi);
+                        d[2 * j] += double(lo);
+                        d[2 * j + 1] += double(hi);
+                        a2[j] = pack(0.f, 0.f);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float lo, hi;
+            unpack(b2[j], lo, hi);
+            d[2 * j] += double(lo);
+            d[2 * j + 1] += double(hi);
+            b2[j] = pack(0.f, 0.f);
+        }
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += d[j];
+    if (s == -1.2345) p.out[0] = s;
+}
+
+template <int PROMO>
+void run_uniform(int sms) {
+    RowParamsF p;
+    cudaMalloc(&p.out, 64);
+    p.groups = (1 << 15) / 128;
+    p.nt = 4;
+    for (int i = 0; i < 128; ++i) p.rc[i][0] = 1.0f - 1e-6f * i, p.rc[i][1] = 1e-3f * i;
+    for (int ctas = 1; ctas <= 2; ++ctas) {
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        float best = 1e9;
+        for (int rep = 0; rep < 4; ++rep) {
+            cudaEventRecord(e0);
+            k_uniform<PROMO><<<sms * ctas, 256>>>(p);
+            cudaEventRecord(e1);
+            cudaEventSynchronize(e1);
+            float ms;
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (ms < best) best = ms;
+        }
+        const double fmas = double(sms) * ctas * 256.0 * (1 << 15) * 16.0;
+        printf("{\"mode\": 7, \"what\": \"row constants in kernel parameters (uniform operands), split accumulators\", \"promote_rows\": %d, \"ctas_per_sm\": %d, \"ms\": %.4f, \"frac_of_fp32_fma_peak\": %.3f}\n",
+               PROMO, ctas, best, fmas / (best * 1e-3) / 1e9 / 35381.0);
+    }
+    cudaFree(p.out);
+}
+
 template <int MODE, int PROMO>
 void run(int sms, const char* what) {
     double* d;
@@ -196,6 +282,8 @@ int main() {
     run<2, 8>(sms, "FFMA2 row loop, fp64 promotion every 8 rows");
     run<6, 16>(sms, "FFMA2 row loop, split accumulators, fp64 promotion every 16 rows");
     run<6, 32>(sms, "FFMA2 row loop, split accumulators, fp64 promotion every 32 rows");
+    run_uniform<16>(sms);
+    run_uniform<32>(sms);
     run<3, 16>(sms, "FFMA2 row loop, packed fp32 TwoSum every 16 rows, fp64 every 128");
     run<3, 8>(sms, "FFMA2 row loop, packed fp32 TwoSum every 8 rows, fp64 every 128");
     return 0;
