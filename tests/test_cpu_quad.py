@@ -25,6 +25,16 @@ def test_sin_closed_form(rule, ev, n):
     assert abs(v - ref) <= 4e-16 * max(abs(ref), 1.0), (v, ref)
 
 
+@pytest.mark.parametrize("n,rule", [((1 << 29) + 12345, "trap"), ((1 << 30) + 999, "mid")])
+def test_sin_closed_form_with_several_tiles_per_part(n, rule):
+    """Full 32-row tiles, three to seven per part: whole and partial flush groups of the fused fp64 loop
+    (column-side rotation once per group, row constants shared by all groups: PartWorker::run_uniform
+    and its mirror in cpu_backend.cpp), and the group with the ragged last tile on the general path."""
+    r = bq.integrate_result("sin", 0.0, math.pi, n, rule, eval="rotate", backend="cpu")
+    ref = oracle_sin(0.0, math.pi, n, rule)
+    assert r.status == 0 and abs(r.value - ref) <= 1e-15 * ref
+
+
 def test_reference_riemann_value():
     # riemann.cpp prints 2.00000000000222 at n=1e9 with one worker (rel. err 1.1e-12);
     # the true left sum is 2 - 1.6e-18.  We must be far closer than the reference.
