@@ -33,7 +33,10 @@
 //   fused 2-DFMA loop (fp64, SinF):    8: 7274, 16: 7374, 32: 7429; a second accumulator set per
 //   column (16 / 8 rows): 7200 / 7079.  Pinning the column constants to aligned register quads
 //   (so that constant and accumulator of a DFMA sit in different register banks) changed
-//   nothing (7421): the loop is not limited by register-bank conflicts.
+//   nothing (7421): the loop is not limited by register-bank conflicts.  What it WAS limited by is
+//   the number of register operands per DFMA: with the row constants as uniform-register operands
+//   (PartWorker::run_uniform, fused fp64) the same two FMAs per sample run at 8 625.  BQ_ROT_UNROLL
+//   now only shapes the general path (row bases from shared memory).
 #ifndef BQ_ROT_UNROLL
 #define BQ_ROT_UNROLL 16
 #endif

@@ -1,5 +1,7 @@
-# fp32 ROTATE: the build in the tree against variants (b1 = the 16-row scheme before error diffusion)
-for v in ${VARIANTS:-b1 tree}; do
+# fp32 ROTATE speed and error: the build in the tree ("tree") against other builds of the library under
+# build/variants/<name>/ (tools/build_variant.py; e.g. one built from an older checkout).
+#   VARIANTS="tree" bash tools/fp32_ab.sh
+for v in ${VARIANTS:-tree}; do
   if [ "$v" = tree ]; then unset B200QUAD_LIB; else export B200QUAD_LIB=build/variants/$v/libb200quad.so; fi
   V=$v python - <<'PY'
 import math, json, os
