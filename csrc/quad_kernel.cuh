@@ -154,7 +154,12 @@ struct PartWorker {
                 }
                 dx[j] = double(threadIdx.x + kThreads * j) * h;
             }
-            sincos(f.angle(double(lane) * double(kWidth) * h), &rowrot.s, &rowrot.c);
+            if constexpr (kUniformRows) {
+                // row r of a tile is row r of a flush group: the host's constant (the general path only)
+                rowrot = SinCos{rowc->cs[lane][1], rowc->cs[lane][0]};
+            } else {
+                sincos(f.angle(double(lane) * double(kWidth) * h), &rowrot.s, &rowrot.c);
+            }
             if constexpr (RowDiffusion<R, kFused>::kOn) {
                 // the four sums over the CTA's 2048 columns, once per launch: warp butterflies, then the
                 // 8 warp sums in order (cpu_backend.cpp does the same); owed[0..3] the totals, owed[4..] scratch
