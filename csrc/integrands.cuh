@@ -162,6 +162,7 @@ struct SinF {
     BQ_HD double fuse_alpha() const { return 1.0; }
     BQ_HD double fuse_beta() const { return 0.0; }
     BQ_HD double fuse_gamma() const { return 0.0; }
+    BQ_HD double fuse_delta() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return bq_sin(x); }
     BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }   // |x| <= kFastTrigMax (plan)
@@ -183,6 +184,7 @@ struct AccF {
     BQ_HD double fuse_alpha() const { return -ascale; }
     BQ_HD double fuse_beta() const { return 0.0; }
     BQ_HD double fuse_gamma() const { return 0.0; }
+    BQ_HD double fuse_delta() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return -(bq_sin(x / R(tscale)) * R(ascale)); }
     BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }
@@ -204,6 +206,7 @@ struct VelF {
     BQ_HD double fuse_alpha() const { return 0.0; }
     BQ_HD double fuse_beta() const { return -vscale; }
     BQ_HD double fuse_gamma() const { return vscale; }
+    BQ_HD double fuse_delta() const { return 0.0; }
     template <class R>
     BQ_HD R eval(R x) const { return (-bq_cos(x / R(tscale)) + R(1)) * R(vscale); }
     BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }
@@ -219,11 +222,15 @@ struct VelF {
 };
 
 struct DisF {
-    static constexpr bool kFusedSum = false;
-    BQ_HD double fuse_alpha() const { return 0.0; }
+    // vscale * x - vscale * tscale * sin(x / tscale): the sine part goes through the fused loop sample by
+    // sample; the linear part, like a constant part, is summed in closed form over the grid
+    // (delta * sum of the x_i, an arithmetic series in dd arithmetic: finish_result)
+    static constexpr bool kFusedSum = true;
+    BQ_HD double fuse_alpha() const { return -(vscale * tscale); }
     BQ_HD double fuse_beta() const { return 0.0; }
     BQ_HD double fuse_gamma() const { return 0.0; }
-    static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = true;
+    BQ_HD double fuse_delta() const { return vscale; }
+    static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = false;
     double tscale, vscale, inv_tscale;
     template <class R>
     BQ_HD R eval(R x) const { return R(vscale) * bq_fma(-R(tscale), bq_sin(x / R(tscale)), x); }

@@ -412,6 +412,18 @@ BQ_HDI ProfileF make_functor<ProfileF>(const Plan& P, const double* t) { return 
 // pairs in index order, scale by h, add the trapezoid end correction
 // (trap = left + h/2 (f(b) - f(a)); the reference has no trapezoid, only the
 // commented-out include at 4main.c:38).
+// sum over the grid of x_i = a + (i + off) * h, i < n:  n * a + h * (n (n - 1) / 2 + n * off), as a pair.
+// n < 2^53 and off is 0, 1/2 or 1, so every factor below is exact and the two products are exact pairs.
+BQ_HDI dd grid_sum_x(const Plan& P) {
+    const double n = double(P.n);
+    const bool odd = (P.n & 1ull) != 0ull;                  // one of n, n - 1 is even: halve that one
+    const double u = odd ? n : n * 0.5;
+    const double v = odd ? double(P.n - 1) * 0.5 : double(P.n - 1);
+    dd tri = dd_mul_d(dd{u, 0.0}, v);                       // n (n - 1) / 2
+    tri = dd_add_d(tri, n * P.off);
+    return dd_add(dd_mul_d(tri, P.h), dd_mul_d(dd{n, 0.0}, P.a));
+}
+
 template <class F>
 BQ_HDI void finish_result(const Plan& P, const F& f, const double* seg_hi, const double* seg_lo,
                           bq_result* out) {
@@ -419,6 +431,10 @@ BQ_HDI void finish_result(const Plan& P, const F& f, const double* seg_hi, const
     for (int s = 0; s < kSegments; ++s) acc = dd_add(acc, dd{seg_hi[s], seg_lo[s]});
     if (F::kFusedSum && P.eval == BQ_EVAL_ROTATE && f.fuse_gamma() != 0.0)
         acc = dd_add(acc, dd_mul_d(dd{double(P.n), 0.0}, f.fuse_gamma()));   // the constant term of every sample
+    if constexpr (F::kFusedSum) {
+        if (P.eval == BQ_EVAL_ROTATE && f.fuse_delta() != 0.0)
+            acc = dd_add(acc, dd_mul_d(grid_sum_x(P), f.fuse_delta()));      // the linear term of every sample
+    }
     dd val = dd_mul_d(acc, P.h);
     if (P.rule == BQ_RULE_TRAP) {
         const bool fast = (P.flags & kFlagFastTrig) != 0;   // same sin/cos as the samples: host == device bits
