@@ -163,6 +163,7 @@ struct SinF {
     BQ_HD double fuse_beta() const { return 0.0; }
     BQ_HD double fuse_gamma() const { return 0.0; }
     BQ_HD double fuse_delta() const { return 0.0; }
+    BQ_HD double fuse_scale() const { return 1.0; }
     template <class R>
     BQ_HD R eval(R x) const { return bq_sin(x); }
     BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }   // |x| <= kFastTrigMax (plan)
@@ -185,6 +186,7 @@ struct AccF {
     BQ_HD double fuse_beta() const { return 0.0; }
     BQ_HD double fuse_gamma() const { return 0.0; }
     BQ_HD double fuse_delta() const { return 0.0; }
+    BQ_HD double fuse_scale() const { return 1.0; }
     template <class R>
     BQ_HD R eval(R x) const { return -(bq_sin(x / R(tscale)) * R(ascale)); }
     BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }
@@ -207,6 +209,7 @@ struct VelF {
     BQ_HD double fuse_beta() const { return -vscale; }
     BQ_HD double fuse_gamma() const { return vscale; }
     BQ_HD double fuse_delta() const { return 0.0; }
+    BQ_HD double fuse_scale() const { return 1.0; }
     template <class R>
     BQ_HD R eval(R x) const { return (-bq_cos(x / R(tscale)) + R(1)) * R(vscale); }
     BQ_HD double eval_fast_d(double x) const { return trig_eval_fast(*this, x); }
@@ -225,11 +228,15 @@ struct DisF {
     // vscale * x - vscale * tscale * sin(x / tscale): the sine part goes through the fused loop sample by
     // sample; the linear part, like a constant part, is summed in closed form over the grid
     // (delta * sum of the x_i, an arithmetic series in dd arithmetic: finish_result)
+    // f = scale * (alpha * sin + delta * x) with alpha = -tscale, delta = 1, scale = vscale: no product of
+    // two parameters is rounded before the two sums meet (x and tscale * sin cancel to x^3 / (6 tscale^2)
+    // for small x; a rounded vscale * tscale cost 4e-12 there)
     static constexpr bool kFusedSum = true;
-    BQ_HD double fuse_alpha() const { return -(vscale * tscale); }
+    BQ_HD double fuse_alpha() const { return -tscale; }
     BQ_HD double fuse_beta() const { return 0.0; }
     BQ_HD double fuse_gamma() const { return 0.0; }
-    BQ_HD double fuse_delta() const { return vscale; }
+    BQ_HD double fuse_delta() const { return 1.0; }
+    BQ_HD double fuse_scale() const { return vscale; }
     static constexpr bool kTrig = true, kNeedS = true, kNeedC = false, kNeedX = false;
     double tscale, vscale, inv_tscale;
     template <class R>

@@ -434,6 +434,7 @@ BQ_HDI void finish_result(const Plan& P, const F& f, const double* seg_hi, const
     if constexpr (F::kFusedSum) {
         if (P.eval == BQ_EVAL_ROTATE && f.fuse_delta() != 0.0)
             acc = dd_add(acc, dd_mul_d(grid_sum_x(P), f.fuse_delta()));      // the linear term of every sample
+        if (P.eval == BQ_EVAL_ROTATE && f.fuse_scale() != 1.0) acc = dd_mul_d(acc, f.fuse_scale());
     }
     dd val = dd_mul_d(acc, P.h);
     if (P.rule == BQ_RULE_TRAP) {

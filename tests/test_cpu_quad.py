@@ -105,7 +105,22 @@ def test_fp32_rotate_on_a_fine_grid_is_accurate_to_fp64_level(a, b, n, rule):
     assert abs(r.value - ref) <= 1e-12 * abs(ref)
 
 
-@pytest.mark.parametrize("name,a,b", [("vel", 0.0, 1800.0), ("acc", 5.0, 900.0), ("vel", 100.0, 700.0)])
+def test_dis_linear_part_in_closed_form_matches_per_sample_evaluation():
+    """ROTATE sums the linear part of dis as an arithmetic series (quad_core.cuh: grid_sum_x) and only the
+    sine part sample by sample; DIRECT forms every sample.  Same tree otherwise: the two agree to an ulp."""
+    for a, b, n, rule in ((0.0, 1800.0, (1 << 24) + 5, "mid"), (100.0, 1500.0, 1 << 25, "trap"),
+                          (-50.0, 900.0, 12_345_678, "right"), (3.0, 4.0, 10_000_019, "left")):
+        r = bq.integrate_result("dis", a, b, n, rule, eval="rotate", backend="cpu")
+        d = bq.integrate_result("dis", a, b, n, rule, eval="direct", backend="cpu")
+        assert r.eval == "rotate" and d.eval == "direct"
+        # x and tscale * sin(x / tscale) cancel for small x (to x^3 / (6 tscale^2)): the bound is an ulp of
+        # the terms that cancel, vscale * |x| per sample, not of their difference
+        cancel = 67.7777777 * max(abs(a), abs(b)) * (b - a)
+        assert abs(r.value - d.value) <= 4e-16 * (abs(d.value) + cancel), (r.value, d.value)
+
+
+@pytest.mark.parametrize("name,a,b", [("vel", 0.0, 1800.0), ("acc", 5.0, 900.0), ("vel", 100.0, 700.0),
+                                      ("dis", 0.0, 1800.0)])
 def test_fp32_rotate_train_models_match_fp64(name, a, b):
     """-ascale * sin and vscale - vscale * cos run the fused fp32 loop on the integrand divided by its
     amplitude (quad_core.cuh: fused_norm; the cos type with its two streams swapped), so the unit
