@@ -46,7 +46,7 @@ def test_fp32_rotate_tracks_fp64_on_any_interval(n, rule, name, a, width):
 
 @settings(max_examples=25, deadline=None, derandomize=True)
 @given(n=st.integers(min_value=1, max_value=200_000), rule=st.sampled_from(RULES),
-       name=st.sampled_from(["sin", "vel", "profile"]), world=st.sampled_from([2, 4, 8]))
+       name=st.sampled_from(["sin", "vel", "dis", "profile"]), world=st.sampled_from([2, 4, 8]))
 def test_any_world_size_reassembles_the_same_bits(n, rule, name, world):
     """Segments computed rank by rank (as the ranks of a world would) fold to the single-rank bits."""
     lib, _ = _native.load()
