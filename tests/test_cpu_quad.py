@@ -35,6 +35,29 @@ def test_sin_closed_form_with_several_tiles_per_part(n, rule):
     assert r.status == 0 and abs(r.value - ref) <= 1e-15 * ref
 
 
+def test_row_constants_follow_the_job():
+    """The row constants of the fused fp64 loop are cached per thread for the last (step, time scale)
+    (host_common.cpp: fill_row_consts): calls that alternate between grids and time scales must each
+    get their own."""
+    import ctypes as C
+    lib, _ = _native.load()
+
+    def vel(tscale, n):
+        job = bq.make_job("vel", 0.0, 900.0, n, "mid", "fp64", "rotate", params=(tscale, 0.0, 67.7777777, 0.0))
+        res = _native.Result()
+        assert lib.bq_cpu_integrate(C.byref(job), 1, C.byref(res)) == 0    # one thread: one cache
+        exact = 67.7777777 * (900.0 - tscale * math.sin(900.0 / tscale))   # integral of vscale * (1 - cos(x / tscale))
+        return res.value, exact
+
+    n1, n2 = (1 << 24) + 3, (1 << 25) + 5          # two grids (4 and 7 rows per tile), same constants' cache
+    seq = [(286.4788975, n1), (100.0, n1), (286.4788975, n1), (100.0, n2), (286.4788975, n2)]
+    for tscale, n in seq:
+        got, exact = vel(tscale, n)
+        assert abs(got - exact) <= 1e-11 * abs(exact), (tscale, n, got, exact)   # midpoint rule error ~ h^2
+    s = bq.integrate_result("sin", 0.0, math.pi, n1, "mid", eval="rotate", backend="cpu")
+    assert abs(s.value - oracle_sin(0.0, math.pi, n1, "mid")) <= 2e-15
+
+
 def test_reference_riemann_value():
     # riemann.cpp prints 2.00000000000222 at n=1e9 with one worker (rel. err 1.1e-12);
     # the true left sum is 2 - 1.6e-18.  We must be far closer than the reference.
